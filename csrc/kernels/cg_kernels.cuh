@@ -1,0 +1,44 @@
+// Launch wrappers of the CG kernels (definitions in cg_kernels.cu, spmv_tma.cu, pipecg_kernels.cu).
+#pragma once
+#include "dev_common.cuh"
+
+namespace cgb {
+
+enum SpmvMode {
+  kSpmvAlpha = 0,  // classic CG: all-reduce p.Ap, alpha = rho / p.Ap stored on the device
+  kSpmvDot = 1,    // all-reduce in.out, result only in Scalars::last_sum
+  kSpmvPlain = 2   // no reduction at all
+};
+
+struct LaunchCfg {
+  int grid_ew;    // persistent grid of the elementwise kernels
+  int grid_spmv;  // persistent grid of the simple stencil SpMV
+  int grid_csr;
+};
+
+// Occupancy-derived persistent grid sizes for this device.
+int query_launch_cfg(int device, LaunchCfg* cfg);
+// Choose the SpMV work decomposition (ntx, nty, nmc, mchunk) for a layout.
+void choose_spmv_tiling(RankDev& P, int grid_spmv);
+
+// r = b, p = b, x = 0, push p's boundary rows, rho = all-reduce(b.b), thresh, iter = 0.
+cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit,
+                        cudaStream_t s);
+// out = A in (+ reduction according to mode); simple = register-marching kernel.
+cudaError_t launch_spmv_simple(const RankDev& P, const LaunchCfg& c, const double* in, double* out,
+                               int mode, cudaStream_t s);
+cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* in, double* out, int mode,
+                            cudaStream_t s);
+// x += alpha p; r -= alpha Ap; rho' = all-reduce(r.r); convergence test; beta.
+cudaError_t launch_update(const RankDev& P, const LaunchCfg& c, const double* p, cudaStream_t s);
+// p = r + beta p, boundary rows first with P2P push into the neighbours' ghost layers.
+cudaError_t launch_pupdate(const RankDev& P, const LaunchCfg& c, double* p, int exch_buf, cudaStream_t s);
+
+cudaError_t launch_rhs_gen(const RankDev& P, const LaunchCfg& c, int rhs_kind, unsigned long long seed,
+                           cudaStream_t s);
+cudaError_t launch_pad(const cgb_layout_t& L, const double* compact, double* padded, cudaStream_t s);
+cudaError_t launch_unpad(const cgb_layout_t& L, const double* padded, double* compact, cudaStream_t s);
+cudaError_t launch_dot(const double* a, const double* b, long long n, double* out, void* scratch,
+                       cudaStream_t s);
+
+}  // namespace cgb

@@ -1,0 +1,301 @@
+// Device-side foundation shared by every kernel: the per-rank control block that lives at the
+// start of the peer-mapped arena, system-scope flag primitives, the deterministic block/grid
+// reduction and the one-shot P2P all-reduce executed by the last CTA of a producing kernel.
+//
+// Where the reference blocks the host twice per iteration to read a scalar back
+// (cublasDdot CUDACG.cu:304, cublasDnrm2 CUDACG.cu:328, host pointer mode), here the scalar
+// recurrences (alpha, beta, rho, convergence flag) stay in device memory and the cross-GPU sum
+// is a handful of 8-byte P2P stores plus a release flag over NVLink.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "../topo/partition.hpp"
+#include "cgb200.h"
+
+namespace cgb {
+
+constexpr int kRedSlots = 4;          // ring of reduction slots (2 would do)
+constexpr int kMaxGrid = 2048;        // upper bound on CTAs of any persistent kernel
+constexpr int kThreads = 256;         // CTA size of every kernel in this file family
+constexpr size_t kCtrlBytes = 8192;   // control block footprint at arena offset 0
+constexpr size_t kPartialsOff = kCtrlBytes;
+constexpr size_t kPartialsBytes = (size_t)kMaxGrid * 2 * sizeof(double);
+constexpr size_t kExchOff = 65536;    // first exchanged vector; identical on every rank
+
+typedef unsigned long long u64;
+
+struct Scalars {
+  double rho;        // r.r of the current residual (global)
+  double rho_prev;
+  double pAp;
+  double alpha, beta;
+  double r0norm;
+  double thresh;     // absolute threshold on ||r||_2 (tol or tol*||r0||)
+  double rnorm;      // last ||r||_2
+  double tol;
+  double gamma_old, alpha_old, delta;  // pipelined CG recurrences
+  double last_sum[2];                  // last reduction result (standalone ops read this)
+  u64 red_seq;       // sequence number of the next all-reduce this rank will publish
+  u64 halo_seq;      // version of the newest halo this rank has pushed / expects
+  long long timeout_cycles;
+  int tol_mode;
+  int iter;          // completed iterations
+  int done;          // 0 running, 1 converged, 2 maxit, <0 cgb_status
+  int maxit;
+  int cur;           // exchange buffer that holds the current SpMV input
+  int pending_x;     // merged variant: x += alpha*p_old still owed
+  unsigned int ticket_red;
+  unsigned int ticket_halo[CGB_NDIR];
+};
+
+// Peers write red_* and halo_flag with P2P stores; everything from `s` on is rank-local.
+struct Control {
+  u64 red_flag[kRedSlots][CGB_MAX_RANKS];
+  double red_val[kRedSlots][CGB_MAX_RANKS][2];
+  u64 halo_flag[CGB_NDIR];  // [d]: newest version pushed into my ghost layer by neighbour nbr[d]
+  u64 pad_[7];
+  Scalars s;
+};
+static_assert(sizeof(Control) <= kCtrlBytes, "control block overflow");
+
+// Everything a kernel needs to know about this rank and its peers; passed by value.
+struct RankDev {
+  Control* ctrl;
+  Control* peer_ctrl[CGB_MAX_RANKS];  // peer control blocks as mapped in this process
+  int nranks, rank;
+  cgb_layout_t lay;
+  cgb_stencil_t st;
+  int y0, z0;                     // global offset of the owned box
+  int nbr[CGB_NDIR];
+  unsigned nbr_mask;              // bit d set if nbr[d] >= 0
+  double* nbr_exch[2][CGB_NDIR];  // neighbours' exchange buffers (mapped)
+  int nbr_ny[CGB_NDIR], nbr_nz[CGB_NDIR], nbr_py[CGB_NDIR];
+  unsigned halo_expect[CGB_NDIR];  // units to count before the flag for direction d is raised
+  double* exch[2];                 // my exchanged vectors (SpMV input, ping-pong)
+  double *x, *r, *Ap, *b, *s, *z, *pp;
+  double* hist;
+  int hist_cap;
+  double2* partials;
+  // CSR problems
+  const int* csr_rowptr;
+  const int* csr_colind;
+  const double* csr_val;
+  // SpMV work decomposition (host-chosen)
+  int ntx, nty, nmc, mchunk;
+};
+
+// ---- system-scope flag primitives (the MPI_Sendrecv / MPI_Allreduce replacement) ----
+
+__device__ __forceinline__ u64 ld_acquire_sys(const u64* p) {
+  u64 v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(u64* p, u64 v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
+  asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+
+// Spin until *p >= target. Bounded: a dead or diverged peer produces an error, not a hang.
+__device__ __forceinline__ bool spin_until_ge(const u64* p, u64 target, long long timeout_cycles) {
+  if (ld_acquire_sys(p) >= target) return true;
+  const long long t0 = clock64();
+  for (;;) {
+    if (ld_acquire_sys(p) >= target) return true;
+    if (clock64() - t0 > timeout_cycles) return false;
+    __nanosleep(20);
+  }
+}
+
+// ---- deterministic reductions ----
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Sum over the CTA in a fixed tree; result valid in thread 0. smem: >= 2*8 doubles.
+__device__ __forceinline__ void block_sum2(double& a, double& b, double* smem) {
+  a = warp_sum(a);
+  b = warp_sum(b);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();  // smem reuse guard
+  if (l == 0) {
+    smem[w] = a;
+    smem[8 + w] = b;
+  }
+  __syncthreads();
+  if (w == 0) {
+    a = l < (kThreads >> 5) ? smem[l] : 0.0;
+    b = l < (kThreads >> 5) ? smem[8 + l] : 0.0;
+    a = warp_sum(a);
+    b = warp_sum(b);
+  }
+}
+
+// Every CTA contributes (a,b); returns true in ALL threads of the CTA that arrived last, with
+// the grid-wide sums (fixed order => run-to-run bitwise reproducible) in (a,b) of thread 0.
+__device__ __forceinline__ bool grid_sum2_last(double& a, double& b, double2* partials,
+                                               unsigned int* ticket, double* smem) {
+  __shared__ int s_last;
+  block_sum2(a, b, smem);
+  if (threadIdx.x == 0) {
+    __stcg(&partials[blockIdx.x], make_double2(a, b));
+    __threadfence();
+    unsigned int t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!s_last) return false;
+  __threadfence();
+  double sa = 0.0, sb = 0.0;
+  for (unsigned i = threadIdx.x; i < gridDim.x; i += kThreads) {
+    double2 v = __ldcg(&partials[i]);
+    sa += v.x;
+    sb += v.y;
+  }
+  block_sum2(sa, sb, smem);
+  a = sa;
+  b = sb;
+  if (threadIdx.x == 0) *ticket = 0u;
+  return true;
+}
+
+// One-shot all-reduce run by the last CTA of a producing kernel: thread t stores this rank's
+// partial into slot[seq%4][rank] of rank t and raises the matching flag, then waits for rank
+// t's contribution to arrive here. Sums are taken in rank order, so every rank obtains
+// bit-identical scalars (mandatory: all ranks must take the same convergence branch).
+// (a,b) in: this rank's sums in thread 0. out: global sums in thread 0. Returns false on timeout.
+__device__ __forceinline__ bool allreduce2_last_cta(const RankDev& P, double& a, double& b, double* smem) {
+  Scalars& S = P.ctrl->s;
+  if (P.nranks == 1) {
+    if (threadIdx.x == 0) {
+      S.last_sum[0] = a;
+      S.last_sum[1] = b;
+      S.red_seq += 1;
+    }
+    return true;
+  }
+  __shared__ int s_ok;
+  const u64 seq = S.red_seq;
+  const int slot = (int)(seq & (kRedSlots - 1));
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    smem[0] = a;
+    smem[1] = b;
+    s_ok = 1;
+  }
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < P.nranks) {
+    Control* pc = P.peer_ctrl[t];
+    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][0], smem[0]);
+    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][1], smem[1]);
+    st_release_sys(&pc->red_flag[slot][P.rank], seq + 1);
+  }
+  __syncthreads();
+  if (t < P.nranks) {
+    bool ok = spin_until_ge(&P.ctrl->red_flag[slot][t], seq + 1, S.timeout_cycles);
+    if (!ok) s_ok = 0;
+    smem[16 + 2 * t] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][0]);
+    smem[17 + 2 * t] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][1]);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double sa = 0.0, sb = 0.0;
+    for (int q = 0; q < P.nranks; ++q) {
+      sa += smem[16 + 2 * q];
+      sb += smem[17 + 2 * q];
+    }
+    a = sa;
+    b = sb;
+    S.last_sum[0] = sa;
+    S.last_sum[1] = sb;
+    S.red_seq = seq + 1;
+    if (!s_ok) S.done = CGB_ERR_TIMEOUT;
+  }
+  return s_ok != 0;
+}
+
+// ---- halo signalling ----
+
+// Called by all threads of a CTA after it stored `cnt[d]` units into neighbour d's ghost layer.
+// The CTA that completes direction d raises the neighbour's flag with `version`.
+__device__ __forceinline__ void halo_commit(const RankDev& P, const unsigned* cnt_smem, u64 version) {
+  __threadfence_system();  // my remote stores are performed before the counters move
+  __syncthreads();
+  const int d = threadIdx.x;
+  if (d < CGB_NDIR && d != 4 && cnt_smem[d] != 0 && P.nbr[d] >= 0) {
+    Scalars& S = P.ctrl->s;
+    __threadfence();
+    unsigned old = atomicAdd(&S.ticket_halo[d], cnt_smem[d]);
+    if (old + cnt_smem[d] == P.halo_expect[d]) {
+      S.ticket_halo[d] = 0u;
+      __threadfence_system();
+      st_release_sys(&P.peer_ctrl[P.nbr[d]]->halo_flag[dir_opposite(d)], version);
+    }
+  }
+}
+
+// All threads of the CTA return once every existing neighbour's halo of `version` has landed.
+__device__ __forceinline__ bool halo_wait_all(const RankDev& P, u64 version) {
+  __shared__ int s_hok;
+  if (threadIdx.x == 0) s_hok = 1;
+  __syncthreads();
+  const int d = threadIdx.x;
+  if (d < CGB_NDIR && d != 4 && P.nbr[d] >= 0) {
+    if (!spin_until_ge(&P.ctrl->halo_flag[d], version, P.ctrl->s.timeout_cycles)) {
+      s_hok = 0;
+      P.ctrl->s.done = CGB_ERR_TIMEOUT;
+    }
+  }
+  __syncthreads();
+  return s_hok != 0;
+}
+
+// ---- elementwise unit mapping: unit u -> pair of x-cells in owned row (j,k) ----
+
+struct UnitMap {
+  int pw;   // pairs per row
+  int ny;
+};
+__device__ __forceinline__ void unit_to_ijk(const UnitMap& m, unsigned u, int& i, int& j, int& k) {
+  unsigned row = u / (unsigned)m.pw;
+  i = 2 * (int)(u - row * (unsigned)m.pw);
+  k = (int)(row / (unsigned)m.ny);
+  j = (int)(row - (unsigned)k * (unsigned)m.ny);
+}
+
+// Directions a row (j,k) has to be pushed to, as a bit mask over d (before masking with nbr_mask).
+__device__ __forceinline__ unsigned row_push_mask(const cgb_layout_t& L, int j, int k) {
+  // dy candidates: bit0 = -1, bit1 = 0, bit2 = +1
+  unsigned my = 2u | (L.gy && j == 0 ? 1u : 0u) | (L.gy && j == L.ny - 1 ? 4u : 0u);
+  unsigned mz = 2u | (L.gz && k == 0 ? 1u : 0u) | (L.gz && k == L.nz - 1 ? 4u : 0u);
+  unsigned m = 0;
+#pragma unroll
+  for (int dz = 0; dz < 3; ++dz)
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy)
+      if ((my >> dy & 1u) && (mz >> dz & 1u)) m |= 1u << (dy + 3 * dz);
+  return m & ~(1u << 4);
+}
+
+// Index of my owned row (j,k), cell i, inside neighbour d's ghost layer.
+__device__ __forceinline__ int64_t ghost_index(const RankDev& P, int d, int i, int j, int k) {
+  const int dy = dir_dy(d), dz = dir_dz(d);
+  const int jn = dy < 0 ? P.nbr_ny[d] : (dy > 0 ? -1 : j);
+  const int kn = dz < 0 ? P.nbr_nz[d] : (dz > 0 ? -1 : k);
+  return (int64_t)i + (int64_t)P.lay.pitch * ((int64_t)(jn + P.lay.gy) + (int64_t)P.nbr_py[d] * (int64_t)(kn + P.lay.gz));
+}
+
+}  // namespace cgb

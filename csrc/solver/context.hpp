@@ -1,0 +1,60 @@
+// Per-rank GPU context: owns the peer-mappable arena (control block, reduction slots, exchanged
+// vectors), the rank-local work vectors, the stream/events and the captured CUDA graphs.
+// RAII replacement of the reference's pointer list + CLEANUP macro (CUDACG.cu:10-33, 43-72).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <vector>
+
+#include "../kernels/cg_kernels.cuh"
+#include "cgb200.h"
+
+struct cgb_ctx {
+  int device = 0;
+  cgb_stencil_t st{};
+  cgb_partition_t part{};
+  cgb_layout_t lay{};
+  int hist_cap = 0;
+
+  void* arena = nullptr;      // ctrl | partials | exch0 | exch1   (peer visible)
+  size_t arena_bytes = 0;
+  void* local = nullptr;      // x | r | Ap | b | hist              (rank local)
+  size_t local_bytes = 0;
+  void* extra = nullptr;      // s | z | pp                         (pipelined CG, on demand)
+  double* compact_tmp = nullptr;
+  int* d_rowptr = nullptr;    // CSR problems
+  int* d_colind = nullptr;
+  double* d_val = nullptr;
+  long long csr_nnz = 0;
+
+  void* peer_base[CGB_MAX_RANKS] = {};
+  bool peer_is_ipc[CGB_MAX_RANKS] = {};
+  bool peers_dirty = true;
+
+  cgb::RankDev P{};
+  cgb::LaunchCfg cfg{};
+
+  cudaStream_t own_stream = nullptr;
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_poll[2] = {nullptr, nullptr};
+  cgb::Scalars* h_scal = nullptr;  // pinned: 2 polling slots
+  int poll_slot = 0;
+
+  // per-solve state
+  cgb_solve_opts_t opts{};
+  bool active = false;
+  cudaStream_t stream = nullptr;
+  int enqueued = 0;
+  long long launches = 0;
+  long long launches_at_begin = 0;
+  std::map<long long, cudaGraphExec_t> graphs;  // key: variant/impl/length
+  void* tma = nullptr;                          // TMA descriptors (spmv_tma.cu), opaque here
+
+  ~cgb_ctx();
+};
+
+namespace cgb {
+int ctx_finalize_peers(cgb_ctx* c);
+int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s);  // one CG iteration, plain launches
+void ctx_drop_graphs(cgb_ctx* c);
+}  // namespace cgb

@@ -1,0 +1,189 @@
+"""GPU solver: the user-facing object around one per-rank native context.
+
+What the reference does inline in ``main`` — stage A and b (CUDACG.cu:120-153), run the loop
+(:244-352), read x back (:355) — is the ``CGSolver`` life cycle::
+
+    s = CGSolver(Problem.poisson3d(512))            # one rank, current CUDA device
+    s.set_rhs("ones")                               # or a numpy / torch array (host or device)
+    res = s.solve(tol=1e-7, maxit=2000)             # device-resident loop, graphs, no host sync
+    x = s.x()                                       # torch tensor on the device
+
+Multi-GPU: build one solver per rank (``rank``/``nranks``), then
+:func:`cuda_mpi_parallel_b200.parallel.attach_torch_distributed` (torchrun) or
+``attach_single_process``.  Scalars are bit-identical on all ranks, so every rank returns the same
+iteration count and residual history.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional
+
+import numpy as np
+
+from .. import _native as N
+from ..parallel.partition import make_layout, make_partition
+from .problems import Problem, _RHS
+
+_VARIANTS = {"fused": N.VAR_FUSED, "merged": N.VAR_MERGED, "pipelined": N.VAR_PIPELINED}
+_SPMV = {"auto": N.SPMV_AUTO, "simple": N.SPMV_SIMPLE, "tma": N.SPMV_TMA}
+
+
+@dataclass
+class SolveResult:
+    iters: int
+    status: int            # 1 converged, 2 maxit, 0 running, <0 error
+    r0norm: float
+    rnorm: float
+    device_ms: float
+    launches: int
+
+    @property
+    def converged(self) -> bool:
+        return self.status == 1
+
+    @property
+    def iters_per_s(self) -> float:
+        return self.iters / (self.device_ms * 1e-3) if self.device_ms > 0 else float("nan")
+
+
+def _ptr(t) -> int:
+    """Device/host pointer of a torch tensor or numpy array."""
+    if isinstance(t, np.ndarray):
+        return t.ctypes.data
+    return t.data_ptr()
+
+
+class CGSolver:
+    def __init__(self, problem: Problem, rank: int = 0, nranks: int = 1, decomp: int = 1, Py: int = 0,
+                 Pz: int = 0, device: Optional[int] = None, maxit_cap: int = 10000):
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("CGSolver needs a CUDA device (use cpu_cg for the CPU oracle)")
+        self.problem = problem
+        self.rank, self.nranks = rank, nranks
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.part = make_partition(problem, nranks, rank, decomp, Py, Pz)
+        self.layout = make_layout(problem, self.part)
+        self.maxit_cap = maxit_cap
+        L = N.lib()
+        ctx = C.c_void_p()
+        if problem.is_csr:
+            N.check(L.cgb_ctx_create_csr(problem.n, int(problem.val.size), problem.rowptr.ctypes.data,
+                                         problem.colind.ctypes.data, problem.val.ctypes.data, self.device,
+                                         maxit_cap, C.byref(ctx)))
+        else:
+            N.check(L.cgb_ctx_create(C.byref(problem.stencil), C.byref(self.part), self.device, maxit_cap,
+                                     C.byref(ctx)))
+        self._ctx = ctx
+        self._opts = N.SolveOpts()
+        L.cgb_solve_opts_default(C.byref(self._opts))
+        if nranks == 1:
+            N.check(L.cgb_ctx_fabric_reset(self._ctx))
+
+    # ---- life cycle ---------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None):
+            N.lib().cgb_ctx_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def n_local(self) -> int:
+        return int(self.layout.owned)
+
+    def _stream(self, stream=None) -> Optional[int]:
+        import torch
+        if stream is None:
+            stream = torch.cuda.current_stream(self.device)
+        if stream.cuda_stream == 0:
+            # The legacy default stream cannot be captured into graphs: the context then runs on its
+            # private stream, made consistent with torch's work by a synchronise on both sides.
+            stream.synchronize()
+        return C.c_void_p(stream.cuda_stream)
+
+    # ---- data ---------------------------------------------------------------------------
+    def set_rhs(self, b="ones", seed: int = 0, stream=None) -> None:
+        """b: generator name ('ones'|'random'|'manufactured'), or this rank's owned box as a numpy
+        array / torch tensor (host pinned or device), compact with x fastest."""
+        L = N.lib()
+        s = self._stream(stream)
+        if isinstance(b, str):
+            N.check(L.cgb_ctx_set_rhs_generated(self._ctx, _RHS[b], seed, s))
+            return
+        if isinstance(b, np.ndarray):
+            b = np.ascontiguousarray(b, dtype=np.float64)
+            if b.size != self.n_local:
+                raise ValueError(f"rhs has {b.size} entries, rank owns {self.n_local}")
+            N.check(L.cgb_ctx_set_rhs(self._ctx, b.ctypes.data, 0, s))
+            import torch
+            torch.cuda.current_stream(self.device).synchronize()  # pageable source must outlive the copy
+            return
+        import torch
+        assert b.dtype == torch.float64 and b.is_contiguous() and b.numel() == self.n_local
+        N.check(L.cgb_ctx_set_rhs(self._ctx, C.c_void_p(b.data_ptr()), 1 if b.is_cuda else 0, s))
+        self._keep = b  # keep the source alive until the stream has consumed it
+
+    def x(self, out=None, stream=None):
+        """Owned part of the solution as a device tensor (compact, x fastest)."""
+        import torch
+        if out is None:
+            out = torch.empty(self.n_local, dtype=torch.float64, device=f"cuda:{self.device}")
+        N.check(N.lib().cgb_ctx_get_x(self._ctx, C.c_void_p(out.data_ptr()), 1 if out.is_cuda else 0,
+                                      self._stream(stream)))
+        return out
+
+    def history(self, n: int) -> np.ndarray:
+        h = np.zeros(max(n, 0))
+        N.check(N.lib().cgb_ctx_get_history(self._ctx, h.ctypes.data, int(n)))
+        return h
+
+    # ---- solve --------------------------------------------------------------------------
+    def _fill_opts(self, tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream):
+        o = self._opts
+        o.tol = tol
+        o.maxit = maxit
+        o.tol_mode = N.TOL_REL if tol_mode == "rel" else N.TOL_ABS
+        o.variant = _VARIANTS[variant]
+        o.spmv_impl = _SPMV[spmv]
+        o.use_graph = int(use_graph)
+        o.chunk = chunk
+        o.fixed_iters = fixed_iters
+        o.stream = self._stream(stream)
+        return o
+
+    def solve(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "fused",
+              spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0,
+              stream=None) -> SolveResult:
+        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
+        r = N.SolveResult()
+        N.check(N.lib().cgb_solve(self._ctx, C.byref(o), C.byref(r)))
+        return SolveResult(r.iters, r.status, r.r0norm, r.rnorm, r.device_ms, r.launches)
+
+    # Split-phase API (bench.py times `iterate` between CUDA events on the caller's stream).
+    def begin(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "fused",
+              spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0, stream=None):
+        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
+        N.check(N.lib().cgb_solve_begin(self._ctx, C.byref(o)))
+
+    def iterate(self, n: int):
+        N.check(N.lib().cgb_solve_iterate(self._ctx, int(n)))
+
+    def poll(self) -> SolveResult:
+        r = N.SolveResult()
+        N.check(N.lib().cgb_solve_poll(self._ctx, 1, C.byref(r)))
+        return SolveResult(r.iters, r.status, r.r0norm, r.rnorm, r.device_ms, r.launches)
+
+    def finish(self) -> SolveResult:
+        r = N.SolveResult()
+        N.check(N.lib().cgb_solve_finish(self._ctx, C.byref(r)))
+        return SolveResult(r.iters, r.status, r.r0norm, r.rnorm, r.device_ms, r.launches)
+
+    @property
+    def launch_count(self) -> int:
+        return int(N.lib().cgb_ctx_launch_count(self._ctx))

@@ -1,0 +1,77 @@
+"""Tier T1: the CPU oracle against analytic answers and scipy (no GPU)."""
+import numpy as np
+import pytest
+
+from cuda_mpi_parallel_b200 import Problem, cpu_cg, cpu_spmv
+
+
+def test_ref3x3_golden_trace():
+    # Golden trace of CUDACG.cu:248-352 on the reference's own system.
+    p = Problem.ref3x3()
+    s = cpu_cg(p, p.rhs("default"), tol=1e-7, maxit=2000)
+    assert s.iters == 3 and s.converged
+    np.testing.assert_allclose(s.x, [0.5, 0.75, 1.0], atol=1e-12)
+    np.testing.assert_allclose(s.history[:2], [8.073855e-01, 1.673428e-01], rtol=1e-6)
+    assert s.history[2] < 1e-7
+    assert abs(s.r0norm - np.linalg.norm([3.5, 1.5, 2.0])) < 1e-14
+
+
+@pytest.mark.parametrize("prob", [Problem.poisson2d(9, 7), Problem.poisson3d(5, 6, 4), Problem.stencil27(4, 5, 6)])
+def test_stencil_matches_assembled_csr(prob):
+    A = prob.to_scipy()
+    assert (abs(A - A.T)).max() == 0
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal(prob.n)
+    np.testing.assert_allclose(cpu_spmv(prob, x), A @ x, rtol=1e-13, atol=1e-13)
+
+
+@pytest.mark.parametrize("prob", [Problem.poisson2d(16, 12), Problem.poisson3d(8, 7, 6), Problem.stencil27(6, 6, 5)])
+def test_cg_solves_manufactured(prob):
+    b = prob.rhs("manufactured")
+    s = cpu_cg(prob, b, tol=1e-10, maxit=500)
+    assert s.converged
+    np.testing.assert_allclose(s.x, prob.manufactured_solution(), atol=1e-8)
+
+
+def test_cg_matches_scipy_direct():
+    import scipy.sparse.linalg as spla
+    prob = Problem.poisson2d(20, 17)
+    b = prob.rhs("random", seed=3)
+    s = cpu_cg(prob, b, tol=1e-11, maxit=1000)
+    xd = spla.spsolve(prob.to_scipy().tocsc(), b)
+    np.testing.assert_allclose(s.x, xd, atol=1e-9)
+
+
+def test_csr_oracle_equals_stencil_oracle():
+    prob = Problem.poisson3d(6, 5, 7)
+    b = prob.rhs("random", seed=1)
+    s1 = cpu_cg(prob, b, tol=1e-9)
+    rowptr, colind, val = prob.to_csr()
+    pc = Problem.csr(rowptr, colind, val)
+    s2 = cpu_cg(pc, b, tol=1e-9)
+    assert s1.iters == s2.iters
+    np.testing.assert_allclose(s1.history, s2.history, rtol=1e-9)
+
+
+def test_abs_vs_rel_tolerance():
+    prob = Problem.poisson2d(24)
+    b = 100.0 * prob.rhs("ones")
+    sa = cpu_cg(prob, b, tol=1e-6, tol_mode="abs")
+    sr = cpu_cg(prob, b, tol=1e-6, tol_mode="rel")
+    assert sa.rnorm < 1e-6 and sr.rnorm < 1e-6 * sr.r0norm
+    assert sr.iters < sa.iters
+
+
+def test_maxit_falls_through_like_the_reference():
+    prob = Problem.poisson2d(32)
+    s = cpu_cg(prob, prob.rhs("ones"), tol=1e-14, maxit=5)
+    assert s.iters == 5 and not s.converged and len(s.history) == 5
+
+
+def test_pipelined_variant_converges_to_same_solution():
+    prob = Problem.stencil27(8, 8, 8)
+    b = prob.rhs("random", seed=5)
+    c = cpu_cg(prob, b, tol=1e-9)
+    p = cpu_cg(prob, b, tol=1e-9, variant="pipelined")
+    assert p.converged and abs(p.iters - c.iters) <= max(2, c.iters // 10)
+    np.testing.assert_allclose(p.x, c.x, atol=1e-7)
