@@ -28,20 +28,24 @@ struct CpuRank {
 double local_spmv(const cgb_stencil_t& st, const cgb_layout_t& L, const double* in, double* out,
                   const double* dot_with) {
   const int zr = kind_is_3d(st.kind) ? 1 : 0;
+  struct Tap { int dx; int64_t off; double c; };
+  std::vector<Tap> taps;
+  for (int dz = -zr; dz <= zr; ++dz)
+    for (int dy = -1; dy <= 1; ++dy)
+      for (int dx = -1; dx <= 1; ++dx) {
+        double co = stencil_coeff(st, dx, dy, dz);
+        if (co != 0.0) taps.push_back({dx, dx + (int64_t)L.pitch * (dy + (int64_t)L.py * dz), co});
+      }
   double acc = 0.0;
   for (int k = 0; k < L.nz; ++k)
     for (int j = 0; j < L.ny; ++j)
       for (int i = 0; i < L.nx; ++i) {
         int64_t c = lay_index(L, i, j, k);
         double s = 0.0;
-        for (int dz = -zr; dz <= zr; ++dz)
-          for (int dy = -1; dy <= 1; ++dy)
-            for (int dx = -1; dx <= 1; ++dx) {
-              double co = stencil_coeff(st, dx, dy, dz);
-              if (co == 0.0) continue;
-              if (i + dx < 0 || i + dx >= L.nx) continue;
-              s += co * in[c + dx + (int64_t)L.pitch * (dy + (int64_t)L.py * dz)];
-            }
+        for (const Tap& t : taps) {
+          if (i + t.dx < 0 || i + t.dx >= L.nx) continue;  // y/z neighbours come from ghost layers
+          s += t.c * in[c + t.off];
+        }
         out[c] = s;
         if (dot_with) acc += dot_with[c] * s;
       }

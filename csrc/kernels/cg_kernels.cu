@@ -263,13 +263,16 @@ __global__ void __launch_bounds__(kThreads) k_spmv_csr(const __grid_constant__ R
   const int lane = threadIdx.x % G;
   const int gpb = kThreads / G;
   double acc = 0.0;
-  for (int row = blockIdx.x * gpb + threadIdx.x / G; row < n; row += gridDim.x * gpb) {
-    const int e0 = P.csr_rowptr[row], e1 = P.csr_rowptr[row + 1];
+  // The trip count depends only on blockIdx, so every lane of a warp reaches the shuffles.
+  for (int base = blockIdx.x * gpb; base < n; base += gridDim.x * gpb) {
+    const int row = base + threadIdx.x / G;
+    const bool valid = row < n;
+    const int e0 = valid ? P.csr_rowptr[row] : 0, e1 = valid ? P.csr_rowptr[row + 1] : 0;
     double s = 0.0;
     for (int e = e0 + lane; e < e1; e += G) s += P.csr_val[e] * in[P.csr_colind[e]];
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, G);
-    if (lane == 0) {
+    if (valid && lane == 0) {
       out[row] = s;
       acc += in[row] * s;
     }

@@ -437,6 +437,27 @@ extern "C" int cgb_solve_iterate(cgb_ctx* c, int n) {
   return CGB_OK;
 }
 
+// n iterations, each followed by a stream-ordered 8-byte D2H copy of ||r||_2 into host_hist[i]
+// (pinned). This is the reference's per-iteration residual read-back (CUDACG.cu:328) without its
+// host stall: the host never waits, the values simply arrive in order.
+extern "C" int cgb_solve_iterate_streamed(cgb_ctx* c, int n, double* host_hist) {
+  CGB_REQUIRE(c && host_hist && n >= 0, "cgb_solve_iterate_streamed: bad argument");
+  if (!c->active) return fail(CGB_ERR_STATE, "cgb_solve_iterate_streamed before cgb_solve_begin");
+  CGB_CUDA(cudaSetDevice(c->device));
+  const int saved_chunk = c->opts.chunk;
+  c->opts.chunk = 1;
+  int rc = CGB_OK;
+  for (int i = 0; i < n && rc == CGB_OK; ++i) {
+    rc = cgb_solve_iterate(c, 1);
+    if (rc == CGB_OK) {
+      cudaError_t e = cudaMemcpyAsync(host_hist + i, &c->P.ctrl->s.rnorm, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
+      if (e != cudaSuccess) rc = fail(CGB_ERR_CUDA, "cudaMemcpyAsync(rnorm): %s", cudaGetErrorString(e));
+    }
+  }
+  c->opts.chunk = saved_chunk;
+  return rc;
+}
+
 static void fill_result(cgb_ctx* c, const Scalars& s, cgb_solve_result_t* res) {
   res->iters = s.iter;
   res->status = s.done;

@@ -104,6 +104,7 @@ def _declare(lib):
         "cgb_solve": (C.c_int, [vp, P(SolveOpts), P(SolveResult)]),
         "cgb_solve_begin": (C.c_int, [vp, P(SolveOpts)]),
         "cgb_solve_iterate": (C.c_int, [vp, C.c_int]),
+        "cgb_solve_iterate_streamed": (C.c_int, [vp, C.c_int, vp]),
         "cgb_solve_poll": (C.c_int, [vp, C.c_int, P(SolveResult)]),
         "cgb_solve_finish": (C.c_int, [vp, P(SolveResult)]),
         "cgb_ctx_launch_count": (i64, [vp]),

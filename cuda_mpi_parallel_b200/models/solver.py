@@ -174,6 +174,13 @@ class CGSolver:
     def iterate(self, n: int):
         N.check(N.lib().cgb_solve_iterate(self._ctx, int(n)))
 
+    def iterate_streamed(self, n: int, host_hist):
+        """n iterations; after each one ||r||_2 is copied (stream-ordered, 8 bytes) into the pinned
+        host tensor ``host_hist[i]`` — the reference reads this scalar back every iteration
+        (CUDACG.cu:328) but blocks the host to do so."""
+        assert host_hist.is_pinned() and host_hist.numel() >= n
+        N.check(N.lib().cgb_solve_iterate_streamed(self._ctx, int(n), C.c_void_p(host_hist.data_ptr())))
+
     def poll(self) -> SolveResult:
         r = N.SolveResult()
         N.check(N.lib().cgb_solve_poll(self._ctx, 1, C.byref(r)))

@@ -207,6 +207,10 @@ int cgb_solve(cgb_ctx* c, const cgb_solve_opts_t* o, cgb_solve_result_t* res);
 int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o);
 /* Enqueue up to n more iterations without synchronising the host. */
 int cgb_solve_iterate(cgb_ctx* c, int n);
+/* n iterations, each followed by a stream-ordered 8-byte device->host copy of ||r||_2 into
+ * host_hist[i] (pinned memory): the reference's per-iteration residual read-back (CUDACG.cu:328)
+ * without stalling the host. */
+int cgb_solve_iterate_streamed(cgb_ctx* c, int n, double* host_hist);
 /* wait != 0: synchronise the stream first. Fills res from device-resident state. */
 int cgb_solve_poll(cgb_ctx* c, int wait, cgb_solve_result_t* res);
 /* Finalise x for variants that defer the last update; must follow the last iterate. */

@@ -1,0 +1,89 @@
+"""Tiers T0/T3/T4 on one GPU: the solver against the CPU oracle (x, iteration count, history)."""
+import numpy as np
+import pytest
+
+from cuda_mpi_parallel_b200 import CGSolver, Problem, cpu_cg
+
+pytestmark = pytest.mark.gpu
+
+
+def test_ref3x3_matches_reference_answer():
+    # CUDACG.cu:79-82 documents x = (0.5, 0.75, 1.0); 3 iterations.
+    p = Problem.ref3x3()
+    s = CGSolver(p)
+    s.set_rhs(p.rhs("default"))
+    res = s.solve(tol=1e-7, maxit=2000)
+    assert res.status == 1 and res.iters == 3
+    np.testing.assert_allclose(s.x().cpu().numpy(), [0.5, 0.75, 1.0], atol=1e-10)
+    h = s.history(3)
+    np.testing.assert_allclose(h[:2], [8.073855e-01, 1.673428e-01], rtol=1e-6)
+    assert h[2] < 1e-7
+
+
+@pytest.mark.parametrize("prob", [Problem.poisson2d(64, 64), Problem.poisson2d(200, 90), Problem.poisson3d(32, 24, 40), Problem.poisson3d(96, 96, 96),
+                                  Problem.stencil27(24, 24, 24)],
+                         ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
+@pytest.mark.parametrize("use_graph", [True, False])
+def test_solver_history_matches_oracle(prob, use_graph):
+    b = prob.rhs("random", seed=7) if prob.n < 500_000 else np.ones(prob.n)
+    ref = cpu_cg(prob, b, tol=1e-7, maxit=2000)
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-7, maxit=2000, use_graph=use_graph, chunk=7)
+    assert res.status == 1
+    assert abs(res.iters - ref.iters) <= 1
+    n = min(res.iters, ref.iters)
+    h = s.history(n)
+    big = ref.history[:n] > 1e-6 * ref.r0norm
+    np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-8)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6 * max(1.0, np.abs(ref.x).max()))
+    assert res.r0norm == pytest.approx(ref.r0norm, rel=1e-13)
+
+
+def test_generated_rhs_equals_host_rhs_and_repeat_solves_are_bitwise_identical():
+    prob = Problem.poisson3d(48, 40, 36)
+    s = CGSolver(prob)
+    s.set_rhs("random", seed=5)
+    r1 = s.solve(tol=1e-8)
+    h1 = s.history(r1.iters)
+    x1 = s.x().clone()
+    s.set_rhs(prob.rhs("random", seed=5))
+    r2 = s.solve(tol=1e-8)
+    assert r1.iters == r2.iters
+    assert (h1 == s.history(r2.iters)).all()          # bitwise run-to-run
+    assert (x1 == s.x()).all()
+
+
+def test_csr_path_equals_matrix_free_path():
+    prob = Problem.poisson3d(20, 18, 16)
+    rowptr, colind, val = prob.to_csr()
+    b = prob.rhs("random", seed=9)
+    s1 = CGSolver(prob)
+    s1.set_rhs(b)
+    r1 = s1.solve(tol=1e-9)
+    s2 = CGSolver(Problem.csr(rowptr, colind, val))
+    s2.set_rhs(b)
+    r2 = s2.solve(tol=1e-9)
+    assert r1.status == r2.status == 1 and abs(r1.iters - r2.iters) <= 1
+    np.testing.assert_allclose(s1.x().cpu().numpy(), s2.x().cpu().numpy(), atol=1e-8)
+
+
+def test_maxit_and_fixed_iters_and_rel_tolerance():
+    prob = Problem.poisson2d(256, 256)
+    s = CGSolver(prob)
+    s.set_rhs("ones")
+    r = s.solve(tol=1e-14, maxit=10)
+    assert r.status == 2 and r.iters == 10
+    r = s.solve(fixed_iters=33, chunk=10)
+    assert r.iters == 33 and r.launches == 1 + 3 * 33
+    r = s.solve(tol=1e-6, tol_mode="rel", maxit=5000)
+    assert r.status == 1 and r.rnorm < 1e-6 * r.r0norm
+
+
+def test_zero_rhs_and_breakdown_are_reported():
+    prob = Problem.poisson2d(32, 32)
+    s = CGSolver(prob)
+    s.set_rhs(np.zeros(prob.n))
+    r = s.solve()
+    assert r.status == 1 and r.iters == 0
+    assert s.x().abs().max().item() == 0.0
