@@ -110,6 +110,8 @@ def _declare(lib):
         "cgb_ctx_launch_count": (i64, [vp]),
         "cgb_op_scratch_bytes": (C.c_size_t, []),
         "cgb_op_dot": (C.c_int, [vp, vp, i64, vp, vp, vp]),
+        "cgb_op_dot_static": (C.c_int, [vp, vp, i64, vp, vp]),
+        "cgb_op_dot_static_max_n": (C.c_longlong, []),
         "cgb_op_spmv_stencil": (C.c_int, [P(Stencil), P(Layout), vp, vp, vp, vp, C.c_int, vp]),
         "cgb_op_spmv_csr": (C.c_int, [i32, vp, vp, vp, vp, vp, vp, vp, vp]),
         "cgb_op_fused_update": (C.c_int, [P(Layout), dbl, vp, vp, vp, vp, vp, vp, vp]),

@@ -225,6 +225,17 @@ size_t cgb_op_scratch_bytes(void);
 /* out[0] = sum a[i]*b[i], deterministic two-stage tree; scratch from cgb_op_scratch_bytes(). */
 int cgb_op_dot(const double* a, const double* b, int64_t n, double* out, void* scratch,
                void* stream);
+/* No counterpart in the reference. Same result as cgb_op_dot, but allocates nothing and takes no
+ * scratch argument: for callers that may not call cudaMalloc where they need the dot product
+ * (time-critical loops that cannot afford the device-wide synchronisation an allocation implies,
+ * plug-ins whose host framework owns all device memory, out-of-memory/teardown paths). The
+ * scratch is a 65,792-byte __device__ array inside the library, resident on every GPU that
+ * loads it until the process exits. Limit: n <= cgb_op_dot_static_max_n() = 2^28 elements; larger
+ * n returns CGB_ERR_INVALID. The first call on each device resolves the array's device address
+ * (cudaGetSymbolAddress) and should be made before any stream capture. All calls on a device
+ * share the array: calls that overlap on the GPU race and must be serialised by the caller. */
+int cgb_op_dot_static(const double* a, const double* b, int64_t n, double* out, void* stream);
+long long cgb_op_dot_static_max_n(void);
 /* Ap = A p on a padded local box (ghost layers of p must be filled by the caller);
  * dot_out (may be NULL) = p.Ap over owned cells. impl: cgb_spmv_impl. */
 int cgb_op_spmv_stencil(const cgb_stencil_t* st, const cgb_layout_t* lay, const double* p,
