@@ -305,3 +305,13 @@ extern "C" int cgb_cpu_spmv_stencil(const cgb_stencil_t* st, const double* x, do
   gather_x(*st, R, y);
   return CGB_OK;
 }
+
+// out = A in on ONE rank's padded box (ghost layers of `in` filled by the caller); returns in.out
+// over owned cells through dot_out. Used by the multi-process CPU path (gloo) and by tests.
+extern "C" int cgb_cpu_spmv_local(const cgb_stencil_t* st, const cgb_layout_t* lay, const double* in, double* out,
+                                  double* dot_out) {
+  CGB_REQUIRE(st && lay && in && out, "cgb_cpu_spmv_local: NULL argument");
+  double d = local_spmv(*st, *lay, in, out, in);
+  if (dot_out) *dot_out = d;
+  return CGB_OK;
+}

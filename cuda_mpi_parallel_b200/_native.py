@@ -86,6 +86,7 @@ def _declare(lib):
         "cgb_cpu_cg_csr": (C.c_int, [i64, vp, vp, vp, vp, vp, dbl, C.c_int, C.c_int, vp, P(CpuResult)]),
         "cgb_cpu_cg_stencil": (C.c_int, [P(Stencil), C.c_int, C.c_int, C.c_int, C.c_int, vp, vp, dbl, C.c_int,
                                          C.c_int, C.c_int, vp, P(CpuResult)]),
+        "cgb_cpu_spmv_local": (C.c_int, [P(Stencil), P(Layout), vp, vp, P(dbl)]),
         "cgb_cpu_spmv_stencil": (C.c_int, [P(Stencil), vp, vp]),
         "cgb_solve_opts_default": (None, [P(SolveOpts)]),
         "cgb_ctx_create": (C.c_int, [P(Stencil), P(Partition), C.c_int, C.c_int, P(vp)]),

@@ -96,7 +96,11 @@ def _build_lib(name: str, srcs, out: Path, link_extra=(), force=False, verbose=F
 
 
 def build_core(force=False, verbose=False) -> Path:
-    _build_lib("core", _sources(CSRC), LIB, force=force, verbose=verbose)
+    import fcntl
+    BUILD.mkdir(exist_ok=True)
+    with open(BUILD / ".lock", "w") as lk:      # several ranks may import at once
+        fcntl.flock(lk, fcntl.LOCK_EX)
+        _build_lib("core", _sources(CSRC), LIB, force=force, verbose=verbose)
     return LIB
 
 

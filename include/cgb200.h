@@ -132,6 +132,9 @@ int cgb_cpu_cg_csr(int64_t n, const int64_t* rowptr, const int32_t* colind, cons
 int cgb_cpu_cg_stencil(const cgb_stencil_t* st, int nranks, int decomp, int Py, int Pz,
                        const double* b, double* x, double tol, int tol_mode, int maxit, int variant,
                        double* hist, cgb_cpu_result_t* res);
+/* out = A in on one rank's padded box (caller fills the ghost layers); *dot_out = in.out. */
+int cgb_cpu_spmv_local(const cgb_stencil_t* st, const cgb_layout_t* lay, const double* in, double* out,
+                       double* dot_out);
 /* y = A x on global compact arrays. */
 int cgb_cpu_spmv_stencil(const cgb_stencil_t* st, const double* x, double* y);
 

@@ -1,0 +1,74 @@
+"""Worker for the multi-process tests (launched with torch.distributed.run).
+
+    mode cpu : gloo, CPU distributed CG (BASELINE config 1) vs the single-process oracle
+    mode gpu : nccl bootstrap + cudaIpc fabric, GPU solver vs the oracle (one rank per GPU)
+"""
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+
+
+def main():
+    mode, name = sys.argv[1], sys.argv[2]
+    dims = [int(v) for v in sys.argv[3].split("x")]
+    decomp = int(sys.argv[4]) if len(sys.argv) > 4 else 1
+    variant = sys.argv[5] if len(sys.argv) > 5 else "fused"
+    import torch
+    import torch.distributed as dist
+    from cuda_mpi_parallel_b200 import Problem, cpu_cg
+    from cuda_mpi_parallel_b200.parallel.partition import gather_global, make_partition, scatter_global
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    prob = Problem.from_name(name, dims)
+    b = prob.rhs("random", seed=21)
+    part = make_partition(prob, world, rank, decomp)
+    b_local = scatter_global(prob, part, b)
+    if mode == "cpu":
+        dist.init_process_group("gloo")
+        from cuda_mpi_parallel_b200.parallel.cpu_dist import cpu_dist_cg
+        s = cpu_dist_cg(prob, b_local, tol=1e-8, decomp=decomp)
+        iters, hist, x_local, status = s.iters, s.history, s.x_local, int(s.converged)
+    else:
+        local_rank = int(os.environ["LOCAL_RANK"])
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from cuda_mpi_parallel_b200 import CGSolver
+        from cuda_mpi_parallel_b200.parallel import attach_torch_distributed
+        sol = CGSolver(prob, rank=rank, nranks=world, decomp=decomp)
+        attach_torch_distributed(sol)
+        sol.set_rhs(b_local)
+        res = sol.solve(tol=1e-8, chunk=5, variant=variant)
+        # second solve on the same fabric: sequence numbers keep growing, history must repeat bitwise
+        h1 = sol.history(res.iters)
+        res2 = sol.solve(tol=1e-8, chunk=8, variant=variant)
+        assert res2.iters == res.iters and (sol.history(res.iters) == h1).all(), "repeat solve differs"
+        iters, hist, status = res.iters, h1, res.status
+        x_local = sol.x().cpu().numpy()
+    gathered = [None] * world
+    dist.all_gather_object(gathered, (iters, hist.tolist(), x_local.tolist()))
+    ok = True
+    msg = ""
+    if rank == 0:
+        ref = cpu_cg(prob, b, tol=1e-8)
+        parts = [make_partition(prob, world, q, decomp) for q in range(world)]
+        x = gather_global(prob, parts, [np.array(g[2]) for g in gathered])
+        same = all(g[0] == gathered[0][0] and g[1] == gathered[0][1] for g in gathered)   # bit-identical on all ranks
+        n = min(iters, ref.iters)
+        big = ref.history[:n] > 1e-6 * ref.r0norm
+        herr = float(np.max(np.abs(np.array(hist)[:n][big] / ref.history[:n][big] - 1))) if big.any() else 0.0
+        xerr = float(np.abs(x - ref.x).max())
+        ok = bool(status == 1 and same and abs(iters - ref.iters) <= 1 and herr < 1e-8 and xerr < 1e-6)
+        msg = json.dumps({"ok": ok, "iters": iters, "ref_iters": ref.iters, "hist_relerr": herr, "x_err": xerr,
+                          "ranks_identical": same, "world": world})
+        print("MPRESULT " + msg, flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,49 @@
+"""Multi-process tiers: gloo world_size 2/4 on the CPU (runs anywhere); nccl + cudaIpc fabric on >= 2 GPUs."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+def _run(nproc, args, port, timeout=300):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}",
+           "--master-addr", "127.0.0.1", "--master-port", str(port), str(ROOT / "tests" / "mp_worker.py"), *args]
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=env, cwd=ROOT)
+    lines = [l for l in r.stdout.splitlines() if l.startswith("MPRESULT ")]
+    assert r.returncode == 0 and lines, f"worker failed rc={r.returncode}\n{r.stdout[-2000:]}\n{r.stderr[-3000:]}"
+    return json.loads(lines[-1][len("MPRESULT "):])
+
+
+@pytest.mark.parametrize("nproc,name,dims,decomp", [(2, "poisson2d5", "64x64", 1), (4, "poisson3d7", "10x12x16", 2),
+                                                    (4, "stencil3d27", "8x10x12", 2)])
+def test_cpu_distributed_cg_gloo(nproc, name, dims, decomp):
+    # BASELINE config 1: 2D 5-pt 64x64, 2 ranks, CPU path.
+    res = _run(nproc, ["cpu", name, dims, str(decomp)], port=29600 + nproc + decomp)
+    assert res["ok"] and res["ranks_identical"], res
+
+
+def _ngpu():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("name,dims,decomp", [("poisson3d7", "64x48x40", 1), ("poisson2d5", "96x70", 1),
+                                              ("stencil3d27", "40x36x32", 1)])
+def test_gpu_fabric_torchrun(name, dims, decomp):
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nproc = 2 if n < 4 else 4
+    res = _run(nproc, ["gpu", name, dims, str(decomp)], port=29700 + decomp, timeout=240)
+    assert res["ok"] and res["ranks_identical"], res
