@@ -71,14 +71,24 @@ extern "C" int cgb_op_spmv_stencil(const cgb_stencil_t* st, const cgb_layout_t* 
                                    double* dot_out, void* scratch, int impl, void* stream) {
   CGB_REQUIRE(st && lay && p && Ap, "cgb_op_spmv_stencil: NULL argument");
   CGB_REQUIRE(kind_is_stencil(st->kind), "cgb_op_spmv_stencil: not a stencil problem");
-  CGB_REQUIRE(impl == CGB_SPMV_AUTO || impl == CGB_SPMV_SIMPLE, "spmv impl %d not available in this build", impl);
+  CGB_REQUIRE(impl >= CGB_SPMV_AUTO && impl <= CGB_SPMV_TMA, "unknown spmv impl %d", impl);
   cudaStream_t s = (cudaStream_t)stream;
   LaunchCfg* cfg;
   CGB_TRY(get_cfg(&cfg));
   RankDev P;
   CGB_TRY(make_op_rank(st, lay, scratch, blank_scalars(), s, &P));
   choose_spmv_tiling(P, cfg->grid_spmv);
-  CGB_CUDA(launch_spmv_simple(P, *cfg, p, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
+  const bool tma = impl != CGB_SPMV_SIMPLE && spmv_tma_supported(P);
+  if (impl == CGB_SPMV_TMA && !tma) return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV needs a 3D stencil problem");
+  if (tma) {
+    alignas(64) unsigned char map[128];
+    CGB_TRY(spmv_tma_make_map(*lay, p, map));
+    int dev = 0;
+    CGB_CUDA(cudaGetDevice(&dev));
+    CGB_CUDA(launch_spmv_tma(P, dev, map, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
+  } else {
+    CGB_CUDA(launch_spmv_simple(P, *cfg, p, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
+  }
   if (dot_out) CGB_CUDA(cudaMemcpyAsync(dot_out, &P.ctrl->s.last_sum[0], sizeof(double), cudaMemcpyDeviceToDevice, s));
   return CGB_OK;
 }

@@ -124,31 +124,36 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
-// Sum over the CTA in a fixed tree; result valid in thread 0. smem: >= 2*8 doubles.
-__device__ __forceinline__ void block_sum2(double& a, double& b, double* smem) {
+// Sum over a CTA of NT threads in a fixed tree; result valid in thread 0. smem: >= 32 doubles.
+template <int NT>
+__device__ __forceinline__ void block_sum2_t(double& a, double& b, double* smem) {
+  constexpr int NW = NT / 32;
+  static_assert(NT % 32 == 0 && NW <= 16, "block_sum2_t: 1..16 full warps");
   a = warp_sum(a);
   b = warp_sum(b);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   __syncthreads();  // smem reuse guard
   if (l == 0) {
     smem[w] = a;
-    smem[8 + w] = b;
+    smem[16 + w] = b;
   }
   __syncthreads();
   if (w == 0) {
-    a = l < (kThreads >> 5) ? smem[l] : 0.0;
-    b = l < (kThreads >> 5) ? smem[8 + l] : 0.0;
+    a = l < NW ? smem[l] : 0.0;
+    b = l < NW ? smem[16 + l] : 0.0;
     a = warp_sum(a);
     b = warp_sum(b);
   }
 }
+__device__ __forceinline__ void block_sum2(double& a, double& b, double* smem) { block_sum2_t<kThreads>(a, b, smem); }
 
 // Every CTA contributes (a,b); returns true in ALL threads of the CTA that arrived last, with
 // the grid-wide sums (fixed order => run-to-run bitwise reproducible) in (a,b) of thread 0.
-__device__ __forceinline__ bool grid_sum2_last(double& a, double& b, double2* partials,
-                                               unsigned int* ticket, double* smem) {
+template <int NT>
+__device__ __forceinline__ bool grid_sum2_last_t(double& a, double& b, double2* partials, unsigned int* ticket,
+                                                 double* smem) {
   __shared__ int s_last;
-  block_sum2(a, b, smem);
+  block_sum2_t<NT>(a, b, smem);
   if (threadIdx.x == 0) {
     __stcg(&partials[blockIdx.x], make_double2(a, b));
     __threadfence();
@@ -159,16 +164,20 @@ __device__ __forceinline__ bool grid_sum2_last(double& a, double& b, double2* pa
   if (!s_last) return false;
   __threadfence();
   double sa = 0.0, sb = 0.0;
-  for (unsigned i = threadIdx.x; i < gridDim.x; i += kThreads) {
+  for (unsigned i = threadIdx.x; i < gridDim.x; i += NT) {
     double2 v = __ldcg(&partials[i]);
     sa += v.x;
     sb += v.y;
   }
-  block_sum2(sa, sb, smem);
+  block_sum2_t<NT>(sa, sb, smem);
   a = sa;
   b = sb;
   if (threadIdx.x == 0) *ticket = 0u;
   return true;
+}
+__device__ __forceinline__ bool grid_sum2_last(double& a, double& b, double2* partials, unsigned int* ticket,
+                                               double* smem) {
+  return grid_sum2_last_t<kThreads>(a, b, partials, ticket, smem);
 }
 
 // One-shot all-reduce run by the last CTA of a producing kernel: thread t stores this rank's

@@ -64,6 +64,12 @@ int alloc_common(cgb_ctx* c) {
   c->peer_base[c->part.rank] = c->arena;
   CGB_TRY(query_launch_cfg(c->device, &c->cfg));
   if (c->st.kind != CGB_KIND_CSR) choose_spmv_tiling(P, c->cfg.grid_spmv);
+  c->tma_ok = false;
+  if (spmv_tma_supported(P)) {
+    int r0 = spmv_tma_make_map(c->lay, P.exch[0], c->tmap[0]);
+    int r1 = spmv_tma_make_map(c->lay, P.exch[1], c->tmap[1]);
+    c->tma_ok = (r0 == CGB_OK && r1 == CGB_OK);
+  }
   // timeout for peer waits lives in the control block and survives solves
   Scalars init{};
   init.timeout_cycles = kDefaultTimeoutCycles;
@@ -356,6 +362,7 @@ int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
   const RankDev& P = c->P;
   double* p = P.exch[0];
   if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, p, P.Ap, kSpmvAlpha, s));
+  else if (c->tma_ok && c->opts.spmv_impl != CGB_SPMV_SIMPLE) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvAlpha, s));
   else CGB_CUDA(launch_spmv_simple(P, c->cfg, p, P.Ap, kSpmvAlpha, s));
   CGB_CUDA(launch_update(P, c->cfg, p, s));
   CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));
@@ -403,6 +410,8 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   }
   CGB_REQUIRE(c->opts.maxit >= 1 && c->opts.maxit <= c->hist_cap, "maxit %d exceeds the context's hist_cap %d",
               c->opts.maxit, c->hist_cap);
+  if (c->opts.spmv_impl == CGB_SPMV_TMA && !c->tma_ok)
+    return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV is not available for this problem (3D stencils only)");
   CGB_TRY(ctx_finalize_peers(c));
   c->stream = pick_stream(c, o->stream);
   c->launches_at_begin = c->launches;

@@ -48,7 +48,8 @@ struct cgb_ctx {
   long long launches = 0;
   long long launches_at_begin = 0;
   std::map<long long, cudaGraphExec_t> graphs;  // key: variant/impl/length
-  void* tma = nullptr;                          // TMA descriptors (spmv_tma.cu), opaque here
+  alignas(64) unsigned char tmap[2][128] = {};  // CUtensorMap of exch[0], exch[1] (spmv_tma.cu)
+  bool tma_ok = false;
 
   ~cgb_ctx();
 };

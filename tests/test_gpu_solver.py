@@ -23,13 +23,13 @@ def test_ref3x3_matches_reference_answer():
 @pytest.mark.parametrize("prob", [Problem.poisson2d(64, 64), Problem.poisson2d(200, 90), Problem.poisson3d(32, 24, 40), Problem.poisson3d(96, 96, 96),
                                   Problem.stencil27(24, 24, 24)],
                          ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
-@pytest.mark.parametrize("use_graph", [True, False])
-def test_solver_history_matches_oracle(prob, use_graph):
+@pytest.mark.parametrize("use_graph,spmv", [(True, "auto"), (False, "auto"), (True, "simple")])
+def test_solver_history_matches_oracle(prob, use_graph, spmv):
     b = prob.rhs("random", seed=7) if prob.n < 500_000 else np.ones(prob.n)
     ref = cpu_cg(prob, b, tol=1e-7, maxit=2000)
     s = CGSolver(prob)
     s.set_rhs(b)
-    res = s.solve(tol=1e-7, maxit=2000, use_graph=use_graph, chunk=7)
+    res = s.solve(tol=1e-7, maxit=2000, use_graph=use_graph, chunk=7, spmv=spmv)
     assert res.status == 1
     assert abs(res.iters - ref.iters) <= 1
     n = min(res.iters, ref.iters)
