@@ -124,23 +124,23 @@ __device__ __forceinline__ double warp_sum(double v) {
   return v;
 }
 
-// Sum over a CTA of NT threads in a fixed tree; result valid in thread 0. smem: >= 32 doubles.
+// Sum over a CTA of NT threads in a fixed tree; result valid in thread 0. smem: >= 64 doubles.
 template <int NT>
 __device__ __forceinline__ void block_sum2_t(double& a, double& b, double* smem) {
   constexpr int NW = NT / 32;
-  static_assert(NT % 32 == 0 && NW <= 16, "block_sum2_t: 1..16 full warps");
+  static_assert(NT % 32 == 0 && NW <= 32, "block_sum2_t: 1..32 full warps");
   a = warp_sum(a);
   b = warp_sum(b);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   __syncthreads();  // smem reuse guard
   if (l == 0) {
     smem[w] = a;
-    smem[16 + w] = b;
+    smem[32 + w] = b;
   }
   __syncthreads();
   if (w == 0) {
     a = l < NW ? smem[l] : 0.0;
-    b = l < NW ? smem[16 + l] : 0.0;
+    b = l < NW ? smem[32 + l] : 0.0;
     a = warp_sum(a);
     b = warp_sum(b);
   }
