@@ -358,11 +358,19 @@ static int launches_per_iter(const cgb_ctx* c) {
   }
 }
 
+// AUTO: the TMA band kernel for the 7-point stencil (measured faster, profiles/), the L1-path
+// kernel for 27-point (the band kernel is issue-bound there) and for shapes it does not cover.
+static bool use_tma(const cgb_ctx* c) {
+  if (!c->tma_ok || c->opts.spmv_impl == CGB_SPMV_SIMPLE) return false;
+  if (c->opts.spmv_impl == CGB_SPMV_TMA) return true;
+  return c->st.kind == CGB_KIND_POISSON3D7;
+}
+
 int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
   const RankDev& P = c->P;
   double* p = P.exch[0];
   if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, p, P.Ap, kSpmvAlpha, s));
-  else if (c->tma_ok && c->opts.spmv_impl != CGB_SPMV_SIMPLE) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvAlpha, s));
+  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvAlpha, s));
   else CGB_CUDA(launch_spmv_simple(P, c->cfg, p, P.Ap, kSpmvAlpha, s));
   CGB_CUDA(launch_update(P, c->cfg, p, s));
   CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));

@@ -39,7 +39,8 @@ def _ngpu():
 @pytest.mark.gpu
 @pytest.mark.multigpu
 @pytest.mark.parametrize("name,dims,decomp", [("poisson3d7", "64x48x40", 1), ("poisson2d5", "96x70", 1),
-                                              ("stencil3d27", "40x36x32", 1)])
+                                              ("stencil3d27", "40x36x32", 1), ("poisson3d7", "96x50x44", 2),
+                                              ("stencil3d27", "36x42x38", 2), ("poisson3d7", "512x64x48", 1)])
 def test_gpu_fabric_torchrun(name, dims, decomp):
     n = _ngpu()
     if n < 2:
