@@ -155,7 +155,7 @@ def main():
         ms = e0.elapsed_time(e1)
         launches = solver.launch_count - l0
         res = solver.finish()
-    assert res.iters == W + K and res.status == 2, f"bench solve did not run the requested iterations: {res}"
+    assert res.iters == W + K and res.status in (0, 2), f"bench solve did not run the requested iterations: {res}"
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

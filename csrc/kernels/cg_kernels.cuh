@@ -38,6 +38,10 @@ cudaError_t launch_update(const RankDev& P, const LaunchCfg& c, const double* p,
 // p = r + beta p, boundary rows first with P2P push into the neighbours' ghost layers.
 cudaError_t launch_pupdate(const RankDev& P, const LaunchCfg& c, double* p, int exch_buf, cudaStream_t s);
 
+// Pipelined CG (pipecg_kernels.cu): wbuf = exchange buffer holding the current w.
+cudaError_t launch_pipe_start(const RankDev& P, const LaunchCfg& c, int wbuf, cudaStream_t s);
+cudaError_t launch_pipe_update(const RankDev& P, const LaunchCfg& c, int wbuf, cudaStream_t s);
+
 cudaError_t launch_rhs_gen(const RankDev& P, const LaunchCfg& c, int rhs_kind, unsigned long long seed,
                            cudaStream_t s);
 cudaError_t launch_pad(const cgb_layout_t& L, const double* compact, double* padded, cudaStream_t s);

@@ -37,6 +37,7 @@ struct Scalars {
   double tol;
   double gamma_old, alpha_old, delta;  // pipelined CG recurrences
   double last_sum[2];                  // last reduction result (standalone ops read this)
+  u64 pub_seq;       // pipelined CG: sequence number of the reduction published by the last update
   u64 red_seq;       // sequence number of the next all-reduce this rank will publish
   u64 halo_seq;      // version of the newest halo this rank has pushed / expects
   long long timeout_cycles;
@@ -234,6 +235,58 @@ __device__ __forceinline__ bool allreduce2_last_cta(const RankDev& P, double& a,
     if (!s_ok) S.done = CGB_ERR_TIMEOUT;
   }
   return s_ok != 0;
+}
+
+// Split-phase variant for pipelined CG: the last CTA of the producing kernel only PUBLISHES
+// (no wait), so the following SpMV runs while the 16-byte messages cross NVLink ...
+__device__ __forceinline__ void allreduce2_publish(const RankDev& P, double a, double b, double* smem) {
+  Scalars& S = P.ctrl->s;
+  const u64 seq = S.red_seq;
+  const int slot = (int)(seq & (kRedSlots - 1));
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    smem[0] = a;
+    smem[1] = b;
+  }
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < P.nranks) {
+    Control* pc = P.peer_ctrl[t];
+    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][0], smem[0]);
+    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][1], smem[1]);
+    st_release_sys(&pc->red_flag[slot][P.rank], seq + 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    S.pub_seq = seq;
+    S.red_seq = seq + 1;
+  }
+}
+
+// ... and every CTA of the consuming kernel completes it: wait for all ranks' contributions of
+// `seq`, sum in rank order (bit-identical everywhere). All threads return the sums.
+__device__ __forceinline__ bool allreduce2_consume(const RankDev& P, u64 seq, double& a, double& b, double* smem) {
+  __shared__ int s_cok;
+  const int slot = (int)(seq & (kRedSlots - 1));
+  if (threadIdx.x == 0) s_cok = 1;
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < P.nranks) {
+    if (!spin_until_ge(&P.ctrl->red_flag[slot][t], seq + 1, P.ctrl->s.timeout_cycles)) s_cok = 0;
+    smem[2 * t] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][0]);
+    smem[2 * t + 1] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][1]);
+  }
+  __syncthreads();
+  double sa = 0.0, sb = 0.0;
+  for (int q = 0; q < P.nranks; ++q) {
+    sa += smem[2 * q];
+    sb += smem[2 * q + 1];
+  }
+  a = sa;
+  b = sb;
+  const bool ok = s_cok != 0;
+  __syncthreads();
+  return ok;
 }
 
 // ---- halo signalling ----

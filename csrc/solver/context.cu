@@ -286,6 +286,20 @@ extern "C" int cgb_ctx_set_rhs_generated(cgb_ctx* c, int rhs_kind, uint64_t seed
   return CGB_OK;
 }
 
+// z, s, p of pipelined CG (three more rank-local vectors), allocated on first use.
+static int ensure_extra(cgb_ctx* c) {
+  if (c->extra) return CGB_OK;
+  const size_t vec_bytes = (size_t)c->lay.vec_elems * sizeof(double);
+  CGB_CUDA(cudaMalloc(&c->extra, 3 * vec_bytes));
+  CGB_CUDA(cudaMemset(c->extra, 0, 3 * vec_bytes));
+  char* e = (char*)c->extra;
+  c->P.z = (double*)e;
+  c->P.s = (double*)(e + vec_bytes);
+  c->P.pp = (double*)(e + 2 * vec_bytes);
+  cgb::ctx_drop_graphs(c);  // captured kernels hold a copy of P
+  return CGB_OK;
+}
+
 static int ensure_compact_tmp(cgb_ctx* c) {
   if (!c->compact_tmp) CGB_CUDA(cudaMalloc(&c->compact_tmp, (size_t)c->lay.owned * sizeof(double)));
   return CGB_OK;
@@ -354,6 +368,7 @@ namespace cgb {
 static int launches_per_iter(const cgb_ctx* c) {
   switch (c->opts.variant) {
     case CGB_VAR_FUSED: return 3;
+    case CGB_VAR_PIPELINED: return 2;
     default: return 3;
   }
 }
@@ -366,19 +381,33 @@ static bool use_tma(const cgb_ctx* c) {
   return c->st.kind == CGB_KIND_POISSON3D7;
 }
 
+static int enqueue_spmv(cgb_ctx* c, int buf, int mode, cudaStream_t s) {
+  const RankDev& P = c->P;
+  if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[buf], P.Ap, mode, s));
+  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[buf], P.Ap, mode, s));
+  else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[buf], P.Ap, mode, s));
+  return CGB_OK;
+}
+
 int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
   const RankDev& P = c->P;
+  if (c->opts.variant == CGB_VAR_PIPELINED) {
+    CGB_TRY(enqueue_spmv(c, c->host_cur, kSpmvPlain, s));            // q = A w
+    CGB_CUDA(launch_pipe_update(P, c->cfg, c->host_cur, s));         // consumes (gamma,delta), publishes the next
+    c->host_cur ^= 1;
+    return CGB_OK;
+  }
   double* p = P.exch[0];
-  if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, p, P.Ap, kSpmvAlpha, s));
-  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvAlpha, s));
-  else CGB_CUDA(launch_spmv_simple(P, c->cfg, p, P.Ap, kSpmvAlpha, s));
+  CGB_TRY(enqueue_spmv(c, 0, kSpmvAlpha, s));
   CGB_CUDA(launch_update(P, c->cfg, p, s));
   CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));
   return CGB_OK;
 }
 
 static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
-  long long key = ((long long)c->opts.variant << 48) | ((long long)c->opts.spmv_impl << 40) | (long long)len;
+  long long key = ((long long)c->opts.variant << 48) | ((long long)c->opts.spmv_impl << 40) |
+                  ((long long)c->host_cur << 36) | (long long)len;
+  const int saved_cur = c->host_cur;
   auto it = c->graphs.find(key);
   if (it != c->graphs.end()) {
     *out = it->second;
@@ -389,6 +418,7 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
   int rc = CGB_OK;
   for (int i = 0; i < len && rc == CGB_OK; ++i) rc = ctx_enqueue_iteration(c, c->stream);
   cudaError_t e = cudaStreamEndCapture(c->stream, &g);
+  c->host_cur = saved_cur;  // capturing executes nothing
   if (rc != CGB_OK) {
     if (g) cudaGraphDestroy(g);
     return rc;
@@ -407,7 +437,8 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
 
 extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c && o, "cgb_solve_begin: NULL argument");
-  CGB_REQUIRE(o->variant == CGB_VAR_FUSED, "variant %d not available in this build", o->variant);
+  CGB_REQUIRE(o->variant == CGB_VAR_FUSED || o->variant == CGB_VAR_PIPELINED, "variant %d not available in this build",
+              o->variant);
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
   if (c->opts.chunk < 1) c->opts.chunk = 25;
@@ -423,8 +454,22 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_TRY(ctx_finalize_peers(c));
   c->stream = pick_stream(c, o->stream);
   c->launches_at_begin = c->launches;
+  if (c->opts.variant == CGB_VAR_PIPELINED) CGB_TRY(ensure_extra(c));
   CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit, c->stream));
   c->launches += 1;
+  c->host_cur = 0;
+  c->iters_target = c->opts.maxit;
+  if (c->opts.variant == CGB_VAR_PIPELINED) {
+    // w0 = A r0 (r0 = b sits in exchange buffer 0 after k_init), then the first (gamma, delta)
+    const RankDev& P = c->P;
+    if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.exch[1], kSpmvPlain, c->stream));
+    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.exch[1], kSpmvPlain, c->stream));
+    else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.exch[1], kSpmvPlain, c->stream));
+    CGB_CUDA(launch_pipe_start(P, c->cfg, 1, c->stream));
+    c->launches += 2;
+    c->host_cur = 1;
+    c->iters_target = c->opts.maxit + 1;  // the last update only records ||r|| of iteration maxit
+  }
   CGB_CUDA(cudaEventRecord(c->ev_begin, c->stream));
   c->enqueued = 0;
   c->active = true;
@@ -441,6 +486,7 @@ extern "C" int cgb_solve_iterate(cgb_ctx* c, int n) {
       cudaGraphExec_t ge;
       CGB_TRY(get_graph(c, chunk, &ge));
       CGB_CUDA(cudaGraphLaunch(ge, c->stream));
+      if (c->opts.variant == CGB_VAR_PIPELINED) c->host_cur ^= (chunk & 1);
       n -= chunk;
       c->enqueued += chunk;
       c->launches += (long long)chunk * launches_per_iter(c);
@@ -520,7 +566,7 @@ extern "C" int cgb_solve_finish(cgb_ctx* c, cgb_solve_result_t* res) {
 extern "C" int cgb_solve(cgb_ctx* c, const cgb_solve_opts_t* o, cgb_solve_result_t* res) {
   CGB_REQUIRE(c && o && res, "cgb_solve: NULL argument");
   CGB_TRY(cgb_solve_begin(c, o));
-  const int chunk = c->opts.chunk, maxit = c->opts.maxit;
+  const int chunk = c->opts.chunk, maxit = c->iters_target;
   int slot = 0;
   bool pending[2] = {false, false};
   auto enqueue_chunk = [&]() -> int {

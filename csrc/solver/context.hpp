@@ -45,6 +45,8 @@ struct cgb_ctx {
   bool active = false;
   cudaStream_t stream = nullptr;
   int enqueued = 0;
+  int host_cur = 0;      // exchange buffer holding the SpMV input of the next enqueued iteration
+  int iters_target = 0;  // iterations the host must enqueue for a full-length solve
   long long launches = 0;
   long long launches_at_begin = 0;
   std::map<long long, cudaGraphExec_t> graphs;  // key: variant/impl/length

@@ -87,3 +87,27 @@ def test_zero_rhs_and_breakdown_are_reported():
     r = s.solve()
     assert r.status == 1 and r.iters == 0
     assert s.x().abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("prob", [Problem.stencil27(24, 24, 24), Problem.poisson3d(40, 36, 44), Problem.poisson2d(120, 90)],
+                         ids=lambda p: p.name)
+def test_pipelined_cg_matches_classic(prob):
+    # Ghysels-Vanroose pipelined CG is algebraically classic CG: same x, iteration count within 10 %,
+    # history equal to the CPU pipelined oracle up to rounding drift.
+    b = prob.rhs("random", seed=13)
+    ref_c = cpu_cg(prob, b, tol=1e-8)
+    ref_p = cpu_cg(prob, b, tol=1e-8, variant="pipelined")
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-8, variant="pipelined", chunk=6)
+    assert res.status == 1
+    assert abs(res.iters - ref_c.iters) <= max(2, ref_c.iters // 10)
+    assert abs(res.iters - ref_p.iters) <= 2
+    n = min(res.iters, ref_p.iters)
+    h = s.history(n)
+    big = ref_p.history[:n] > 1e-5 * ref_p.r0norm
+    np.testing.assert_allclose(h[big], ref_p.history[:n][big], rtol=1e-5)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref_c.x, atol=1e-6)
+    r2 = s.solve(tol=1e-14, maxit=7, variant="pipelined", chunk=4)
+    assert r2.status == 2 and r2.iters == 7
+    assert s.history(7)[6] > 0

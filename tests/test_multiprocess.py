@@ -48,3 +48,16 @@ def test_gpu_fabric_torchrun(name, dims, decomp):
     nproc = 2 if n < 4 else 4
     res = _run(nproc, ["gpu", name, dims, str(decomp)], port=29700 + decomp, timeout=240)
     assert res["ok"] and res["ranks_identical"], res
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("name,dims,decomp", [("stencil3d27", "40x36x32", 1), ("poisson3d7", "96x50x44", 2),
+                                              ("poisson2d5", "96x70", 1)])
+def test_gpu_fabric_pipelined_cg(name, dims, decomp):
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nproc = 2 if n < 4 else 4
+    res = _run(nproc, ["gpu", name, dims, str(decomp), "pipelined"], port=29720 + decomp, timeout=240)
+    assert res["ok"] and res["ranks_identical"], res
