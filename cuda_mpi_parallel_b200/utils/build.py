@@ -113,14 +113,15 @@ def build_baseline(force=False, verbose=False) -> Path:
 
 
 def build_cli(force=False, verbose=False) -> Path:
+    """The command-line front end: plain C++ on top of the C ABI (no CUDA in this translation unit)."""
     src = ROOT / "tools" / "cgb200_main.cpp"
     if not src.exists():
         return CLI
     CLI.parent.mkdir(exist_ok=True)
-    newest = max(p.stat().st_mtime for p in [src, LIB])
+    newest = max(p.stat().st_mtime for p in [src, LIB, ROOT / "include" / "cgb200.h"])
     if force or not CLI.exists() or CLI.stat().st_mtime < newest:
-        cmd = [nvcc(), *ARCH, "-O2", "-std=c++17", f"-I{ROOT / 'include'}", str(src), "-o", str(CLI),
-               f"-L{LIBDIR}", "-lcgb200", "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../cuda_mpi_parallel_b200/lib"]
+        cmd = ["g++", "-O2", "-std=c++17", "-Wall", f"-I{ROOT / 'include'}", str(src), "-o", str(CLI),
+               f"-L{LIBDIR}", "-lcgb200", "-Wl,-rpath,$ORIGIN/../cuda_mpi_parallel_b200/lib"]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError(f"CLI build failed:\n{r.stdout}{r.stderr}")

@@ -1,0 +1,96 @@
+"""Tier T0: the command-line front end against the reference's literal stdout."""
+import json
+import subprocess
+
+import numpy as np
+import pytest
+
+from cuda_mpi_parallel_b200 import Problem, cpu_cg
+from cuda_mpi_parallel_b200.utils import build
+
+REFERENCE_STDOUT = "0.500000\n0.750000\n1.000000\nSuccess\n"   # CUDACG.cu:361-365
+
+
+@pytest.fixture(scope="module")
+def cli():
+    build.build_core()
+    return str(build.build_cli())
+
+
+def run(cli, *args):
+    return subprocess.run([cli, *args], capture_output=True, text=True, timeout=300)
+
+
+def test_cpu_variant_reproduces_reference_stdout(cli):
+    r = run(cli, "--variant", "cpu")
+    assert r.returncode == 0 and r.stdout == REFERENCE_STDOUT and r.stderr == ""
+
+
+def test_failure_contract_one_line_exit_1(cli):
+    r = run(cli, "--problem", "nonsense")
+    assert r.returncode == 1 and r.stdout.count("\n") == 1 and r.stderr == ""
+
+
+def test_baseline_config1_cpu_two_ranks_history_file(cli, tmp_path):
+    # BASELINE config 1: 2D 5-point Poisson 64x64, 2 ranks, CPU path.
+    h, j, xo = tmp_path / "h.txt", tmp_path / "j.json", tmp_path / "x.txt"
+    r = run(cli, "--variant", "cpu", "--problem", "poisson2d5", "--n", "64,64", "--gpus", "2", "--hist-out", str(h),
+            "--json-out", str(j), "--x-out", str(xo))
+    assert r.returncode == 0 and r.stdout == "Success\n"
+    prob = Problem.poisson2d(64, 64)
+    ref = cpu_cg(prob, prob.rhs("ones"))
+    rows = [l.split() for l in h.read_text().splitlines()]
+    assert [int(a) for a, _ in rows] == list(range(1, ref.iters + 1))
+    np.testing.assert_allclose([float(b) for _, b in rows], ref.history, rtol=1e-9)
+    meta = json.loads(j.read_text())
+    assert meta["iters"] == ref.iters and meta["status"] == 1
+    np.testing.assert_allclose(np.loadtxt(xo), ref.x, atol=1e-9)
+
+
+def test_matrix_market_input(cli, tmp_path):
+    m = tmp_path / "a.mtx"
+    m.write_text("%%MatrixMarket matrix coordinate real symmetric\n% the reference matrix, lower triangle\n"
+                 "3 3 4\n1 1 3.0\n3 1 2.0\n2 2 2.0\n3 3 1.0\n")
+    r = run(cli, "--variant", "cpu", "--problem", f"csr:{m}")
+    assert r.returncode == 0
+    got = [float(v) for v in r.stdout.split()[:3]]
+    A = np.array([[3, 0, 2], [0, 2, 0], [2, 0, 1.0]])
+    np.testing.assert_allclose(got, np.linalg.solve(A, np.ones(3)), atol=1e-5)
+
+
+@pytest.mark.gpu
+def test_gpu_default_run_reproduces_reference_stdout(cli):
+    r = run(cli)
+    assert r.returncode == 0 and r.stdout == REFERENCE_STDOUT, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_gpu_stencil_run_matches_oracle(cli, tmp_path):
+    h = tmp_path / "h.txt"
+    r = run(cli, "--problem", "poisson3d7", "--n", "40,36,44", "--rhs", "random:3", "--hist-out", str(h), "--tol", "1e-8")
+    assert r.returncode == 0 and r.stdout == "Success\n", r.stdout
+    prob = Problem.poisson3d(40, 36, 44)
+    ref = cpu_cg(prob, prob.rhs("random", seed=3), tol=1e-8)
+    hist = np.array([float(l.split()[1]) for l in h.read_text().splitlines()])
+    assert abs(len(hist) - ref.iters) <= 1
+    n = min(len(hist), ref.iters)
+    big = ref.history[:n] > 1e-6 * ref.r0norm
+    np.testing.assert_allclose(hist[:n][big], ref.history[:n][big], rtol=1e-8)
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_gpu_single_process_multi_gpu(cli, tmp_path):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    P = 4 if torch.cuda.device_count() >= 4 else 2
+    for variant, decomp in (("fused", "1d"), ("pipelined", "2d" if P == 4 else "1d")):
+        h = tmp_path / f"h_{variant}.txt"
+        r = run(cli, "--problem", "stencil3d27", "--n", "36,40,44", "--gpus", str(P), "--decomp", decomp, "--variant",
+                variant, "--hist-out", str(h), "--tol", "1e-8", "--rhs", "random:4")
+        assert r.returncode == 0 and r.stdout == "Success\n", r.stdout + r.stderr
+        prob = Problem.stencil27(36, 40, 44)
+        ref = cpu_cg(prob, prob.rhs("random", seed=4), tol=1e-8)
+        hist = np.array([float(l.split()[1]) for l in h.read_text().splitlines()])
+        assert abs(len(hist) - ref.iters) <= 2
