@@ -342,24 +342,7 @@ __global__ void __launch_bounds__(kThreads) k_update(const __grid_constant__ Ran
   double a = acc, z = 0.0;
   if (grid_sum2_last(a, z, P.partials, &S.ticket_red, red_smem)) {
     bool ok = allreduce2_last_cta(P, a, z, red_smem);
-    if (threadIdx.x == 0 && ok) {
-      const double rn = sqrt(a);
-      const int it = S.iter;
-      if (it < P.hist_cap) P.hist[it] = rn;
-      S.rnorm = rn;
-      S.iter = it + 1;
-      if (!isfinite(a)) {
-        S.done = CGB_ERR_BREAKDOWN;
-      } else if (rn < S.thresh) {
-        S.done = 1;
-      } else {
-        S.beta = a / S.rho;
-        S.rho_prev = S.rho;
-        S.rho = a;
-        if (it + 1 >= S.maxit) S.done = 2;
-        else S.halo_seq += 1;  // version the following k_pupdate will publish
-      }
-    }
+    if (threadIdx.x == 0 && ok) cg_after_rr(P, a);
   }
 }
 

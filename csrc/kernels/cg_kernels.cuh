@@ -7,7 +7,10 @@ namespace cgb {
 enum SpmvMode {
   kSpmvAlpha = 0,  // classic CG: all-reduce p.Ap, alpha = rho / p.Ap stored on the device
   kSpmvDot = 1,    // all-reduce in.out, result only in Scalars::last_sum
-  kSpmvPlain = 2   // no reduction at all
+  kSpmvPlain = 2,  // no reduction at all
+  // TMA kernel only ("recompute" variant): trade a second stencil evaluation for 16 B/DOF
+  kSpmvAlphaNoStore = 3,  // like kSpmvAlpha but Ap is never written
+  kSpmvUpdate = 4         // recompute Ap from p; x += alpha p; r -= alpha Ap; r.r -> test, beta
 };
 
 struct LaunchCfg {

@@ -289,6 +289,30 @@ __device__ __forceinline__ bool allreduce2_consume(const RankDev& P, u64 seq, do
   return ok;
 }
 
+// What the last CTA does once the global r.r of an x/r update is known: record ||r||, apply the
+// reference's stopping test (absolute ||r||_2 < tol, after the x/r update and before the p update,
+// CUDACG.cu:333), compute beta (CUDACG.cu:339), bump the iteration counter and announce the halo
+// version the following p-update will publish. Thread 0 only.
+__device__ __forceinline__ void cg_after_rr(const RankDev& P, double rr) {
+  Scalars& S = P.ctrl->s;
+  const double rn = sqrt(rr);
+  const int it = S.iter;
+  if (it < P.hist_cap) P.hist[it] = rn;
+  S.rnorm = rn;
+  S.iter = it + 1;
+  if (!isfinite(rr)) {
+    S.done = CGB_ERR_BREAKDOWN;
+  } else if (rn < S.thresh) {
+    S.done = 1;
+  } else {
+    S.beta = rr / S.rho;
+    S.rho_prev = S.rho;
+    S.rho = rr;
+    if (it + 1 >= S.maxit) S.done = 2;
+    else S.halo_seq += 1;
+  }
+}
+
 // ---- halo signalling ----
 
 // Called by all threads of a CTA after it stored `cnt[d]` units into neighbour d's ghost layer.

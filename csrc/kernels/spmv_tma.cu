@@ -114,9 +114,12 @@ __device__ __forceinline__ void plane_from_slab(const unsigned char* slab, const
   }
 }
 
-template <int KIND>
+// OUT: 0 store Ap and accumulate p.Ap; 1 accumulate p.Ap only; 2 x += alpha p, r -= alpha Ap,
+// accumulate r.r (x/r pairs were prefetched one plane ahead into vx/vr).
+template <int KIND, int OUT>
 __device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out, const PS2& pv, const PS2& cu,
-                                     const PS2& nx, int i, int j, int jend, int k, double& acc) {
+                                     const PS2& nx, int i, int j, int jend, int k, double alpha, double2 vx, double2 vr,
+                                     double& acc) {
   const cgb_layout_t& L = P.lay;
   if (j >= jend) return;
   const double cc = P.st.c_center, cf = P.st.c_face;
@@ -128,13 +131,28 @@ __device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out,
     a1 += ce * (cu.s2[1] + (pv.s1[1] + nx.s1[1])) + cn * (pv.s2[1] + nx.s2[1]);
   }
   const int64_t idx = lay_index(L, i, j, k);
-  if (i + 1 < L.nx) {
-    *reinterpret_cast<double2*>(out + idx) = make_double2(a0, a1);
-    acc += cu.s0[0] * a0 + cu.s0[1] * a1;
-  } else {
-    out[idx] = a0;
-    acc += cu.s0[0] * a0;
+  const bool pair = i + 1 < L.nx;
+  if (OUT == 2) {
+    vx.x += alpha * cu.s0[0];
+    vr.x -= alpha * a0;
+    if (pair) {
+      vx.y += alpha * cu.s0[1];
+      vr.y -= alpha * a1;
+      *reinterpret_cast<double2*>(P.x + idx) = vx;
+      *reinterpret_cast<double2*>(P.r + idx) = vr;
+      acc += vr.x * vr.x + vr.y * vr.y;
+    } else {
+      P.x[idx] = vx.x;
+      P.r[idx] = vr.x;
+      acc += vr.x * vr.x;
+    }
+    return;
   }
+  if (OUT == 0) {
+    if (pair) *reinterpret_cast<double2*>(out + idx) = make_double2(a0, a1);
+    else out[idx] = a0;
+  }
+  acc += cu.s0[0] * a0 + (pair ? cu.s0[1] * a1 : 0.0);
 }
 
 struct Item {
@@ -154,7 +172,7 @@ __device__ __forceinline__ Item make_item(const RankDev& P, const BandGeo& G, in
   return it;
 }
 
-template <int KIND>
+template <int KIND, int OUT>
 __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ RankDev P,
                                                       const __grid_constant__ CUtensorMap tmap,
                                                       const __grid_constant__ BandGeo G, double* __restrict__ out,
@@ -178,6 +196,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
   const bool nb_zlo = P.nbr[dir_index(0, -1)] >= 0, nb_zhi = P.nbr[dir_index(0, 1)] >= 0;
   const bool nb_ylo = P.nbr[dir_index(-1, 0)] >= 0, nb_yhi = P.nbr[dir_index(1, 0)] >= 0;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const double alpha = S.alpha;
   double acc = 0.0;
 
   if (warp == kNC / 32) {
@@ -231,16 +250,32 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
       const int nsteps = it.k1 - it.k0 + 2;
       PS2 pa, pb, ca, cb, na, nb;
+      double2 xa = make_double2(0, 0), xb = xa, ra2 = xa, rb2 = xa;  // x/r pairs of the next output plane
       for (int s = 0; s < nsteps; ++s, ++n) {
         const unsigned st = n % kStages, ph = (n / kStages) & 1u;
         mbar_wait(full0 + 8 * st, ph);
         if (active) plane_from_slab<KIND>(smem_raw + (size_t)st * G.stage_bytes, tp, ra, na, nb);
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
+        const double2 cxa = xa, cxb = xb, cra = ra2, crb = rb2;
+        if (OUT == 2 && s >= 1 && s + 1 < nsteps) {
+          // prefetch x and r of the plane that is emitted at step s+1
+          const int kn = it.dir > 0 ? it.k0 + s - 1 : it.k1 - s;
+          if (ja < jend) {
+            const int64_t ia = lay_index(L, i, ja, kn);
+            xa = *reinterpret_cast<const double2*>(P.x + ia);
+            ra2 = *reinterpret_cast<const double2*>(P.r + ia);
+          }
+          if (ja + 1 < jend) {
+            const int64_t ib = lay_index(L, i, ja + 1, kn);
+            xb = *reinterpret_cast<const double2*>(P.x + ib);
+            rb2 = *reinterpret_cast<const double2*>(P.r + ib);
+          }
+        }
         if (s >= 2) {
           const int k = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
-          emit<KIND>(P, out, pa, ca, na, i, ja, jend, k, acc);
-          emit<KIND>(P, out, pb, cb, nb, i, ja + 1, jend, k, acc);
+          emit<KIND, OUT>(P, out, pa, ca, na, i, ja, jend, k, alpha, cxa, cra, acc);
+          emit<KIND, OUT>(P, out, pb, cb, nb, i, ja + 1, jend, k, alpha, cxb, crb, acc);
         }
         pa = ca; pb = cb;
         ca = na; cb = nb;
@@ -250,10 +285,14 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
   if (mode == kSpmvPlain) return;
   double a = acc, z = 0.0;
   if (grid_sum2_last_t<kNT>(a, z, P.partials, &S.ticket_red, red_smem)) {
-    allreduce2_last_cta(P, a, z, red_smem);
-    if (threadIdx.x == 0 && mode == kSpmvAlpha) {
-      S.pAp = a;
-      S.alpha = S.rho / a;
+    const bool ok = allreduce2_last_cta(P, a, z, red_smem);
+    if (threadIdx.x == 0) {
+      if (OUT == 2) {
+        if (ok) cg_after_rr(P, a);
+      } else if (mode == kSpmvAlpha || mode == kSpmvAlphaNoStore) {
+        S.pAp = a;
+        S.alpha = S.rho / a;
+      }
     }
   }
 }
@@ -335,11 +374,14 @@ int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out) {
 cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, double* out, int mode, cudaStream_t s) {
   static bool attr_set[64] = {};
   if (device >= 0 && device < 64 && !attr_set[device]) {
-    cudaError_t e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON3D7>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         220 * 1024);
-    if (e == cudaSuccess)
-      e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               220 * 1024);
+    const int lim = 220 * 1024;
+    const auto at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    cudaError_t e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON3D7, 0>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON3D7, 1>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON3D7, 2>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27, 0>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27, 1>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27, 2>, at, lim);
     if (e != cudaSuccess) return e;
     attr_set[device] = true;
   }
@@ -350,12 +392,17 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, doubl
   size_t sm;
   if (!make_geo(P, nsm, &G, &grid, &sm)) return cudaErrorInvalidConfiguration;
   const CUtensorMap& tm = *reinterpret_cast<const CUtensorMap*>(map);
-  if (P.st.kind == CGB_KIND_POISSON3D7)
-    k_spmv_tma<CGB_KIND_POISSON3D7><<<grid, kNT, sm, s>>>(P, tm, G, out, mode);
-  else if (P.st.kind == CGB_KIND_STENCIL3D27)
-    k_spmv_tma<CGB_KIND_STENCIL3D27><<<grid, kNT, sm, s>>>(P, tm, G, out, mode);
-  else
-    return cudaErrorInvalidValue;
+  const bool k7 = P.st.kind == CGB_KIND_POISSON3D7;
+  if (!k7 && P.st.kind != CGB_KIND_STENCIL3D27) return cudaErrorInvalidValue;
+#define CGB_TMA_LAUNCH(OUT)                                                                        \
+  do {                                                                                             \
+    if (k7) k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, G, out, mode);        \
+    else k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, G, out, mode);          \
+  } while (0)
+  if (mode == kSpmvUpdate) CGB_TMA_LAUNCH(2);
+  else if (mode == kSpmvAlphaNoStore) CGB_TMA_LAUNCH(1);
+  else CGB_TMA_LAUNCH(0);
+#undef CGB_TMA_LAUNCH
   return cudaGetLastError();
 }
 

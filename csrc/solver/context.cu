@@ -398,6 +398,13 @@ int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
     return CGB_OK;
   }
   double* p = P.exch[0];
+  if (c->opts.variant == CGB_VAR_MERGED) {
+    // 72 B/DOF: Ap is never stored; the update kernel re-evaluates the stencil from the p slabs
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvAlphaNoStore, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvUpdate, s));
+    CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));
+    return CGB_OK;
+  }
   CGB_TRY(enqueue_spmv(c, 0, kSpmvAlpha, s));
   CGB_CUDA(launch_update(P, c->cfg, p, s));
   CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));
@@ -437,8 +444,9 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
 
 extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c && o, "cgb_solve_begin: NULL argument");
-  CGB_REQUIRE(o->variant == CGB_VAR_FUSED || o->variant == CGB_VAR_PIPELINED, "variant %d not available in this build",
-              o->variant);
+  CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_PIPELINED, "unknown variant %d", o->variant);
+  if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
+    return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
   if (c->opts.chunk < 1) c->opts.chunk = 25;

@@ -144,7 +144,8 @@ typedef struct cgb_ctx cgb_ctx;
 
 typedef enum cgb_variant {
   CGB_VAR_FUSED = 0,      /* classic CG, 3 fused kernels/iter (spmv+dot, update+dot, p-update+halo) */
-  CGB_VAR_MERGED = 1,     /* classic CG, 2 kernels/iter: p-update and x-update folded into the SpMV */
+  CGB_VAR_MERGED = 1,     /* classic CG "recompute": Ap is never stored, the x/r update re-evaluates the
+                             stencil from TMA slabs of p (72 instead of 88 B/DOF); 3D stencils, nx <= 512 */
   CGB_VAR_PIPELINED = 2   /* Ghysels-Vanroose, one fused 2-scalar reduction per iteration */
 } cgb_variant;
 

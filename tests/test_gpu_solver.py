@@ -111,3 +111,32 @@ def test_pipelined_cg_matches_classic(prob):
     r2 = s.solve(tol=1e-14, maxit=7, variant="pipelined", chunk=4)
     assert r2.status == 2 and r2.iters == 7
     assert s.history(7)[6] > 0
+
+
+@pytest.mark.parametrize("prob", [Problem.poisson3d(40, 36, 44), Problem.poisson3d(130, 37, 21), Problem.stencil27(24, 28, 24),
+                                  Problem.poisson3d(512, 24, 20)], ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
+def test_recompute_variant_matches_oracle(prob):
+    # 72 B/DOF variant: Ap never stored, x/r update re-evaluates the stencil. Same algorithm, same history.
+    b = prob.rhs("random", seed=17)
+    ref = cpu_cg(prob, b, tol=1e-8)
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-8, variant="recompute", chunk=5)
+    assert res.status == 1 and abs(res.iters - ref.iters) <= 1
+    n = min(res.iters, ref.iters)
+    h = s.history(n)
+    big = ref.history[:n] > 1e-6 * ref.r0norm
+    np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-8)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
+    f = CGSolver(prob)
+    f.set_rhs(b)
+    rf = f.solve(tol=1e-8, variant="fused", spmv="tma")
+    assert rf.iters == res.iters
+
+
+def test_recompute_variant_rejects_unsupported_shapes():
+    from cuda_mpi_parallel_b200._native import NativeError
+    s = CGSolver(Problem.poisson2d(64, 64))
+    s.set_rhs("ones")
+    with pytest.raises(NativeError):
+        s.solve(variant="recompute")

@@ -61,3 +61,15 @@ def test_gpu_fabric_pipelined_cg(name, dims, decomp):
     nproc = 2 if n < 4 else 4
     res = _run(nproc, ["gpu", name, dims, str(decomp), "pipelined"], port=29720 + decomp, timeout=240)
     assert res["ok"] and res["ranks_identical"], res
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("name,dims,decomp", [("poisson3d7", "64x48x40", 1), ("stencil3d27", "36x42x38", 2)])
+def test_gpu_fabric_recompute_variant(name, dims, decomp):
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nproc = 2 if n < 4 else 4
+    res = _run(nproc, ["gpu", name, dims, str(decomp), "recompute"], port=29740 + decomp, timeout=240)
+    assert res["ok"] and res["ranks_identical"], res
