@@ -86,7 +86,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "refstyle"])
     ap.add_argument("--problem", default="poisson3d7", choices=["poisson2d5", "poisson3d7", "stencil3d27"])
     ap.add_argument("--grid", type=int, nargs="+", default=None, help="grid extents (default: the headline 512^3)")
-    ap.add_argument("--variant", default=os.environ.get("CGB_VARIANT", "fused"))
+    ap.add_argument("--variant", default=os.environ.get("CGB_VARIANT", "auto"))
     ap.add_argument("--spmv", default=os.environ.get("CGB_SPMV", "auto"))
     ap.add_argument("--decomp", type=int, default=1)
     ap.add_argument("--chunk", type=int, default=0)

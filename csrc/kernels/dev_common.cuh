@@ -51,10 +51,13 @@ struct Scalars {
   unsigned int ticket_halo[CGB_NDIR];
 };
 
-// Peers write red_* and halo_flag with P2P stores; everything from `s` on is rank-local.
+// Peers write red_ll and halo_flag with P2P stores; everything from `s` on is rank-local.
+// red_ll[slot][rank][w]: the two fp64 partials of `rank` as four 8-byte words, each carrying half
+// of a double in its low 32 bits and the reduction's sequence tag in its high 32 bits. An 8-byte
+// store is single-copy atomic, so a word is either the old or the new (value, tag) pair and no
+// fence or separate flag is needed: the reader simply polls until all four tags match.
 struct Control {
-  u64 red_flag[kRedSlots][CGB_MAX_RANKS];
-  double red_val[kRedSlots][CGB_MAX_RANKS][2];
+  u64 red_ll[kRedSlots][CGB_MAX_RANKS][4];
   u64 halo_flag[CGB_NDIR];  // [d]: newest version pushed into my ghost layer by neighbour nbr[d]
   u64 pad_[7];
   Scalars s;
@@ -104,6 +107,38 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double* p) {
 }
 __device__ __forceinline__ void st_relaxed_sys_f64(double* p, double v) {
   asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+
+__device__ __forceinline__ u64 ld_relaxed_sys_u64(const u64* p) {
+  u64 v;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_sys_u64(u64* p, u64 v) {
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// ---- flag-in-data ("LL") messages for the all-reduce ----
+__device__ __forceinline__ void ll_send2(u64* dst4, double a, double b, unsigned tag) {
+  const u64 ua = (u64)__double_as_longlong(a), ub = (u64)__double_as_longlong(b), t = (u64)tag << 32;
+  st_relaxed_sys_u64(dst4 + 0, t | (ua & 0xffffffffull));
+  st_relaxed_sys_u64(dst4 + 1, t | (ua >> 32));
+  st_relaxed_sys_u64(dst4 + 2, t | (ub & 0xffffffffull));
+  st_relaxed_sys_u64(dst4 + 3, t | (ub >> 32));
+}
+__device__ __forceinline__ bool ll_recv2(const u64* src4, unsigned tag, long long timeout_cycles, double& a, double& b) {
+  const long long t0 = clock64();
+  for (;;) {
+    const u64 w0 = ld_relaxed_sys_u64(src4 + 0), w1 = ld_relaxed_sys_u64(src4 + 1);
+    const u64 w2 = ld_relaxed_sys_u64(src4 + 2), w3 = ld_relaxed_sys_u64(src4 + 3);
+    if ((unsigned)(w0 >> 32) == tag && (unsigned)(w1 >> 32) == tag && (unsigned)(w2 >> 32) == tag &&
+        (unsigned)(w3 >> 32) == tag) {
+      a = __longlong_as_double((long long)((w0 & 0xffffffffull) | (w1 << 32)));
+      b = __longlong_as_double((long long)((w2 & 0xffffffffull) | (w3 << 32)));
+      return true;
+    }
+    if (clock64() - t0 > timeout_cycles) return false;
+  }
 }
 
 // Spin until *p >= target. Bounded: a dead or diverged peer produces an error, not a hang.
@@ -207,18 +242,13 @@ __device__ __forceinline__ bool allreduce2_last_cta(const RankDev& P, double& a,
   }
   __syncthreads();
   const int t = threadIdx.x;
+  const unsigned tag = (unsigned)(seq + 1);
   if (t < P.nranks) {
-    Control* pc = P.peer_ctrl[t];
-    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][0], smem[0]);
-    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][1], smem[1]);
-    st_release_sys(&pc->red_flag[slot][P.rank], seq + 1);
-  }
-  __syncthreads();
-  if (t < P.nranks) {
-    bool ok = spin_until_ge(&P.ctrl->red_flag[slot][t], seq + 1, S.timeout_cycles);
-    if (!ok) s_ok = 0;
-    smem[16 + 2 * t] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][0]);
-    smem[17 + 2 * t] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][1]);
+    ll_send2(&P.peer_ctrl[t]->red_ll[slot][P.rank][0], smem[0], smem[1], tag);
+    double va, vb;
+    if (!ll_recv2(&P.ctrl->red_ll[slot][t][0], tag, S.timeout_cycles, va, vb)) s_ok = 0;
+    smem[16 + 2 * t] = va;
+    smem[17 + 2 * t] = vb;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -250,12 +280,7 @@ __device__ __forceinline__ void allreduce2_publish(const RankDev& P, double a, d
   }
   __syncthreads();
   const int t = threadIdx.x;
-  if (t < P.nranks) {
-    Control* pc = P.peer_ctrl[t];
-    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][0], smem[0]);
-    st_relaxed_sys_f64(&pc->red_val[slot][P.rank][1], smem[1]);
-    st_release_sys(&pc->red_flag[slot][P.rank], seq + 1);
-  }
+  if (t < P.nranks) ll_send2(&P.peer_ctrl[t]->red_ll[slot][P.rank][0], smem[0], smem[1], (unsigned)(seq + 1));
   __syncthreads();
   if (threadIdx.x == 0) {
     S.pub_seq = seq;
@@ -272,9 +297,10 @@ __device__ __forceinline__ bool allreduce2_consume(const RankDev& P, u64 seq, do
   __syncthreads();
   const int t = threadIdx.x;
   if (t < P.nranks) {
-    if (!spin_until_ge(&P.ctrl->red_flag[slot][t], seq + 1, P.ctrl->s.timeout_cycles)) s_cok = 0;
-    smem[2 * t] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][0]);
-    smem[2 * t + 1] = ld_relaxed_sys_f64(&P.ctrl->red_val[slot][t][1]);
+    double va, vb;
+    if (!ll_recv2(&P.ctrl->red_ll[slot][t][0], (unsigned)(seq + 1), P.ctrl->s.timeout_cycles, va, vb)) s_cok = 0;
+    smem[2 * t] = va;
+    smem[2 * t + 1] = vb;
   }
   __syncthreads();
   double sa = 0.0, sb = 0.0;
@@ -318,6 +344,11 @@ __device__ __forceinline__ void cg_after_rr(const RankDev& P, double rr) {
 // Called by all threads of a CTA after it stored `cnt[d]` units into neighbour d's ghost layer.
 // The CTA that completes direction d raises the neighbour's flag with `version`.
 __device__ __forceinline__ void halo_commit(const RankDev& P, const unsigned* cnt_smem, u64 version) {
+  __syncthreads();  // counters complete
+  unsigned any = 0;
+#pragma unroll
+  for (int d = 0; d < CGB_NDIR; ++d) any |= cnt_smem[d];
+  if (!any) return;        // CTA-uniform: this CTA pushed nothing
   __threadfence_system();  // my remote stores are performed before the counters move
   __syncthreads();
   const int d = threadIdx.x;

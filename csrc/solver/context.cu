@@ -356,7 +356,7 @@ extern "C" void cgb_solve_opts_default(cgb_solve_opts_t* o) {
   o->tol = 1e-7;                 // CUDACG.cu:245
   o->tol_mode = CGB_TOL_ABS;     // CUDACG.cu:333
   o->maxit = 2000;               // CUDACG.cu:244
-  o->variant = CGB_VAR_FUSED;
+  o->variant = CGB_VAR_AUTO;
   o->spmv_impl = CGB_SPMV_AUTO;
   o->use_graph = 1;
   o->chunk = 25;
@@ -444,11 +444,14 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
 
 extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c && o, "cgb_solve_begin: NULL argument");
-  CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_PIPELINED, "unknown variant %d", o->variant);
+  CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_AUTO, "unknown variant %d", o->variant);
   if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
     return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
+  if (c->opts.variant == CGB_VAR_AUTO)
+    c->opts.variant = (c->tma_ok && c->st.kind == CGB_KIND_POISSON3D7 && o->spmv_impl != CGB_SPMV_SIMPLE) ? CGB_VAR_MERGED
+                                                                                                        : CGB_VAR_FUSED;
   if (c->opts.chunk < 1) c->opts.chunk = 25;
   if (c->opts.fixed_iters > 0) {
     c->opts.maxit = c->opts.fixed_iters;

@@ -25,7 +25,7 @@ from .. import _native as N
 from ..parallel.partition import make_layout, make_partition
 from .problems import Problem, _RHS
 
-_VARIANTS = {"fused": N.VAR_FUSED, "recompute": N.VAR_MERGED, "merged": N.VAR_MERGED, "pipelined": N.VAR_PIPELINED}
+_VARIANTS = {"auto": N.VAR_AUTO, "fused": N.VAR_FUSED, "recompute": N.VAR_MERGED, "merged": N.VAR_MERGED, "pipelined": N.VAR_PIPELINED}
 _SPMV = {"auto": N.SPMV_AUTO, "simple": N.SPMV_SIMPLE, "tma": N.SPMV_TMA}
 
 
@@ -157,7 +157,7 @@ class CGSolver:
         o.stream = self._stream(stream)
         return o
 
-    def solve(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "fused",
+    def solve(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "auto",
               spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0,
               stream=None) -> SolveResult:
         o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
@@ -166,7 +166,7 @@ class CGSolver:
         return SolveResult(r.iters, r.status, r.r0norm, r.rnorm, r.device_ms, r.launches)
 
     # Split-phase API (bench.py times `iterate` between CUDA events on the caller's stream).
-    def begin(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "fused",
+    def begin(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "auto",
               spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0, stream=None):
         o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
         N.check(N.lib().cgb_solve_begin(self._ctx, C.byref(o)))

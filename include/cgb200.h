@@ -146,7 +146,8 @@ typedef enum cgb_variant {
   CGB_VAR_FUSED = 0,      /* classic CG, 3 fused kernels/iter (spmv+dot, update+dot, p-update+halo) */
   CGB_VAR_MERGED = 1,     /* classic CG "recompute": Ap is never stored, the x/r update re-evaluates the
                              stencil from TMA slabs of p (72 instead of 88 B/DOF); 3D stencils, nx <= 512 */
-  CGB_VAR_PIPELINED = 2   /* Ghysels-Vanroose, one fused 2-scalar reduction per iteration */
+  CGB_VAR_PIPELINED = 2,  /* Ghysels-Vanroose, one fused 2-scalar reduction per iteration */
+  CGB_VAR_AUTO = 3        /* MERGED where it applies and is measured faster (7-point 3D), else FUSED */
 } cgb_variant;
 
 typedef enum cgb_spmv_impl {

@@ -7,7 +7,7 @@
 //
 // Everything the reference hard-codes is a flag here:
 //   --problem ref3x3|poisson2d5|poisson3d7|stencil3d27|csr:<file.mtx>     --n NX[,NY[,NZ]]
-//   --gpus P  --decomp 1d|2d[:PYxPZ]   --variant fused|pipelined|cpu   --spmv auto|simple|tma
+//   --gpus P  --decomp 1d|2d[:PYxPZ]   --variant auto|fused|recompute|pipelined|cpu   --spmv auto|simple|tma
 //   --tol T  --tol-mode abs|rel  --maxit N  --rhs ones|random[:seed]|manufactured
 //   --print-x / --no-print-x   --x-out FILE   --hist-out FILE   --json-out FILE   --chunk N
 // stdout stays diffable against the reference; history ("iter ||r||" as "%d %.17e") and the timing
@@ -28,7 +28,7 @@
 namespace {
 
 struct Args {
-  std::string problem = "ref3x3", csr_file, variant = "fused", spmv = "auto", rhs = "ones", x_out, hist_out, json_out;
+  std::string problem = "ref3x3", csr_file, variant = "auto", spmv = "auto", rhs = "ones", x_out, hist_out, json_out;
   int n[3] = {0, 0, 0};
   int gpus = 1, decomp = 1, Py = 0, Pz = 0, maxit = 2000, chunk = 25, tol_mode = CGB_TOL_ABS;
   unsigned long long seed = 0;
@@ -91,7 +91,7 @@ Args parse(int argc, char** argv) {
     else if (f == "--json-out") a.json_out = need(i);
     else if (f == "--help" || f == "-h") {
       std::printf("usage: cgb200 [--problem ref3x3|poisson2d5|poisson3d7|stencil3d27|csr:<file.mtx>] [--n NX[,NY[,NZ]]]\n"
-                  "              [--gpus P] [--decomp 1d|2d[:PYxPZ]] [--variant fused|pipelined|cpu] [--spmv auto|simple|tma]\n"
+                  "              [--gpus P] [--decomp 1d|2d[:PYxPZ]] [--variant auto|fused|recompute|pipelined|cpu] [--spmv auto|simple|tma]\n"
                   "              [--tol T] [--tol-mode abs|rel] [--maxit N] [--rhs ones|random[:seed]|manufactured]\n"
                   "              [--print-x|--no-print-x] [--x-out F] [--hist-out F] [--json-out F] [--chunk N]\n");
       std::exit(0);
@@ -239,7 +239,9 @@ int main(int argc, char** argv) {
       o.tol_mode = a.tol_mode;
       o.maxit = a.maxit;
       o.chunk = a.chunk;
-      o.variant = a.variant == "pipelined" ? CGB_VAR_PIPELINED : CGB_VAR_FUSED;
+      o.variant = a.variant == "pipelined" ? CGB_VAR_PIPELINED
+                : a.variant == "fused" ? CGB_VAR_FUSED
+                : a.variant == "recompute" ? CGB_VAR_MERGED : CGB_VAR_AUTO;
       o.spmv_impl = a.spmv == "simple" ? CGB_SPMV_SIMPLE : a.spmv == "tma" ? CGB_SPMV_TMA : CGB_SPMV_AUTO;
       if (P == 1) {
         check(cgb_solve(ctx[0], &o, &res), "solve");
