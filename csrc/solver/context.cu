@@ -8,6 +8,7 @@
 
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 
 #include "../common/status.hpp"
@@ -17,7 +18,13 @@ using namespace cgb;
 
 namespace {
 
-constexpr long long kDefaultTimeoutCycles = 20LL * 1000 * 1000 * 1000;  // ~10 s at 2 GHz
+// Peer waits give up after ~10 s (at 2 GHz); CGB_TIMEOUT_MS overrides (tests use short values).
+long long default_timeout_cycles() {
+  const char* e = std::getenv("CGB_TIMEOUT_MS");
+  const double ms = e ? std::atof(e) : 10000.0;
+  return (long long)(ms * 2.0e6);
+}
+#define kDefaultTimeoutCycles default_timeout_cycles()
 
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -442,8 +449,13 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
 
 }  // namespace cgb
 
-extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
-  CGB_REQUIRE(c && o, "cgb_solve_begin: NULL argument");
+// Everything a solve needs that may allocate or synchronise a device: option checks, the extra
+// vectors of pipelined CG, peer resolution and the iteration graphs. cgb_solve_begin calls it; a
+// driver that runs SEVERAL ranks from one host thread must call it on every rank before the first
+// cgb_solve_begin, because with peer access enabled a cudaMalloc on one device waits for the
+// others, and those would already be spinning on this rank's first message.
+extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
+  CGB_REQUIRE(c && o, "cgb_solve_prepare: NULL argument");
   CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_AUTO, "unknown variant %d", o->variant);
   if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
     return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
@@ -462,10 +474,25 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
               c->opts.maxit, c->hist_cap);
   if (c->opts.spmv_impl == CGB_SPMV_TMA && !c->tma_ok)
     return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV is not available for this problem (3D stencils only)");
+  if (c->opts.variant == CGB_VAR_PIPELINED) CGB_TRY(ensure_extra(c));
   CGB_TRY(ctx_finalize_peers(c));
   c->stream = pick_stream(c, o->stream);
+  if (c->opts.use_graph) {
+    cudaGraphExec_t ge;
+    const int saved = c->host_cur;
+    for (int par = 0; par < (c->opts.variant == CGB_VAR_PIPELINED ? 2 : 1); ++par) {
+      c->host_cur = par;
+      CGB_TRY(get_graph(c, c->opts.chunk, &ge));
+    }
+    c->host_cur = saved;
+  }
+  return CGB_OK;
+}
+
+extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
+  CGB_REQUIRE(c && o, "cgb_solve_begin: NULL argument");
+  CGB_TRY(cgb_solve_prepare(c, o));
   c->launches_at_begin = c->launches;
-  if (c->opts.variant == CGB_VAR_PIPELINED) CGB_TRY(ensure_extra(c));
   CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit, c->stream));
   c->launches += 1;
   c->host_cur = 0;

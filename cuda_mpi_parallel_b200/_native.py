@@ -104,6 +104,7 @@ def _declare(lib):
         "cgb_ctx_get_history": (C.c_int, [vp, vp, C.c_int]),
         "cgb_solve": (C.c_int, [vp, P(SolveOpts), P(SolveResult)]),
         "cgb_solve_begin": (C.c_int, [vp, P(SolveOpts)]),
+        "cgb_solve_prepare": (C.c_int, [vp, P(SolveOpts)]),
         "cgb_solve_iterate": (C.c_int, [vp, C.c_int]),
         "cgb_solve_iterate_streamed": (C.c_int, [vp, C.c_int, vp]),
         "cgb_solve_poll": (C.c_int, [vp, C.c_int, P(SolveResult)]),

@@ -171,6 +171,15 @@ class CGSolver:
         o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
         N.check(N.lib().cgb_solve_begin(self._ctx, C.byref(o)))
 
+    def prepare(self, **kw):
+        """Allocate and capture everything `begin(**kw)` would, without launching. Needed only when one
+        host thread drives several ranks (see cgb_solve_prepare)."""
+        args = dict(tol=1e-7, maxit=2000, tol_mode="abs", variant="auto", spmv="auto", use_graph=True, chunk=25,
+                    fixed_iters=0, stream=None)
+        args.update(kw)
+        o = self._fill_opts(**args)
+        N.check(N.lib().cgb_solve_prepare(self._ctx, C.byref(o)))
+
     def iterate(self, n: int):
         N.check(N.lib().cgb_solve_iterate(self._ctx, int(n)))
 

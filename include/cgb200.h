@@ -210,6 +210,12 @@ int cgb_ctx_get_history(cgb_ctx* c, double* dst, int n);
 /* Solve = begin (init kernel) + iterate* + finish. cgb_solve does all three. */
 int cgb_solve(cgb_ctx* c, const cgb_solve_opts_t* o, cgb_solve_result_t* res);
 int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o);
+/* Does every allocating / device-synchronising part of a solve (extra vectors, graph capture) and
+ * nothing else. cgb_solve_begin calls it. A driver that runs several ranks from ONE host thread
+ * must call it on every rank before the first cgb_solve_begin: with peer access enabled, a
+ * cudaMalloc on one device waits for the other devices, which would already be spinning on this
+ * rank's first message. */
+int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o);
 /* Enqueue up to n more iterations without synchronising the host. */
 int cgb_solve_iterate(cgb_ctx* c, int n);
 /* n iterations, each followed by a stream-ordered 8-byte device->host copy of ||r||_2 into

@@ -247,6 +247,7 @@ int main(int argc, char** argv) {
         check(cgb_solve(ctx[0], &o, &res), "solve");
       } else {
         // one host thread drives all ranks: enqueue a chunk everywhere, then look at the flags
+        for (int r = 0; r < P; ++r) check(cgb_solve_prepare(ctx[(size_t)r], &o), "solve prepare");
         for (int r = 0; r < P; ++r) check(cgb_solve_begin(ctx[(size_t)r], &o), "solve begin");
         const int target = a.maxit + (o.variant == CGB_VAR_PIPELINED ? 1 : 0);
         int enq = 0;
