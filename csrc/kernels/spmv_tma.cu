@@ -118,10 +118,8 @@ __device__ __forceinline__ void plane_from_slab(const unsigned char* slab, const
 // accumulate r.r (x/r pairs were prefetched one plane ahead into vx/vr).
 template <int KIND, int OUT>
 __device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out, const PS2& pv, const PS2& cu,
-                                     const PS2& nx, int i, int j, int jend, int k, double alpha, double2 vx, double2 vr,
+                                     const PS2& nx, int64_t idx, bool pair, double alpha, double2 vx, double2 vr,
                                      double& acc) {
-  const cgb_layout_t& L = P.lay;
-  if (j >= jend) return;
   const double cc = P.st.c_center, cf = P.st.c_face;
   double a0 = cc * cu.s0[0] + cf * (cu.s1[0] + (pv.s0[0] + nx.s0[0]));
   double a1 = cc * cu.s0[1] + cf * (cu.s1[1] + (pv.s0[1] + nx.s0[1]));
@@ -130,8 +128,6 @@ __device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out,
     a0 += ce * (cu.s2[0] + (pv.s1[0] + nx.s1[0])) + cn * (pv.s2[0] + nx.s2[0]);
     a1 += ce * (cu.s2[1] + (pv.s1[1] + nx.s1[1])) + cn * (pv.s2[1] + nx.s2[1]);
   }
-  const int64_t idx = lay_index(L, i, j, k);
-  const bool pair = i + 1 < L.nx;
   if (OUT == 2) {
     vx.x += alpha * cu.s0[0];
     vr.x -= alpha * a0;
@@ -248,7 +244,11 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
       const int ja = it.band * G.RB + ra;
       const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
+      const bool va = ja < jend, vb = ja + 1 < jend, pair = i + 1 < L.nx;
       const int nsteps = it.k1 - it.k0 + 2;
+      const int64_t ps = (int64_t)L.pitch * L.py * it.dir;           // signed plane stride along the sweep
+      // index of (i, ja) on the plane emitted at step 2, then advanced by ps per step
+      int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);
       PS2 pa, pb, ca, cb, na, nb;
       double2 xa = make_double2(0, 0), xb = xa, ra2 = xa, rb2 = xa;  // x/r pairs of the next output plane
       for (int s = 0; s < nsteps; ++s, ++n) {
@@ -260,22 +260,20 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
         const double2 cxa = xa, cxb = xb, cra = ra2, crb = rb2;
         if (OUT == 2 && s >= 1 && s + 1 < nsteps) {
           // prefetch x and r of the plane that is emitted at step s+1
-          const int kn = it.dir > 0 ? it.k0 + s - 1 : it.k1 - s;
-          if (ja < jend) {
-            const int64_t ia = lay_index(L, i, ja, kn);
-            xa = *reinterpret_cast<const double2*>(P.x + ia);
-            ra2 = *reinterpret_cast<const double2*>(P.r + ia);
+          const int64_t in = s >= 2 ? idx + ps : idx;
+          if (va) {
+            xa = *reinterpret_cast<const double2*>(P.x + in);
+            ra2 = *reinterpret_cast<const double2*>(P.r + in);
           }
-          if (ja + 1 < jend) {
-            const int64_t ib = lay_index(L, i, ja + 1, kn);
-            xb = *reinterpret_cast<const double2*>(P.x + ib);
-            rb2 = *reinterpret_cast<const double2*>(P.r + ib);
+          if (vb) {
+            xb = *reinterpret_cast<const double2*>(P.x + in + L.pitch);
+            rb2 = *reinterpret_cast<const double2*>(P.r + in + L.pitch);
           }
         }
         if (s >= 2) {
-          const int k = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
-          emit<KIND, OUT>(P, out, pa, ca, na, i, ja, jend, k, alpha, cxa, cra, acc);
-          emit<KIND, OUT>(P, out, pb, cb, nb, i, ja + 1, jend, k, alpha, cxb, crb, acc);
+          if (va) emit<KIND, OUT>(P, out, pa, ca, na, idx, pair, alpha, cxa, cra, acc);
+          if (vb) emit<KIND, OUT>(P, out, pb, cb, nb, idx + L.pitch, pair, alpha, cxb, crb, acc);
+          idx += ps;
         }
         pa = ca; pb = cb;
         ca = na; cb = nb;
