@@ -85,7 +85,7 @@ extern "C" int cgb_op_spmv_stencil(const cgb_stencil_t* st, const cgb_layout_t* 
     CGB_TRY(spmv_tma_make_map(*lay, p, map));
     int dev = 0;
     CGB_CUDA(cudaGetDevice(&dev));
-    CGB_CUDA(launch_spmv_tma(P, dev, map, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
+    CGB_CUDA(launch_spmv_tma(P, dev, map, nullptr, nullptr, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
   } else {
     CGB_CUDA(launch_spmv_simple(P, *cfg, p, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
   }

@@ -36,7 +36,7 @@ namespace {
 constexpr int BW = 128;                  // cells per TMA box row
 constexpr int kNC = 512;                 // consumer threads
 constexpr int kNT = kNC + 32;            // + one producer warp
-constexpr int kStages = 6;
+constexpr int kMaxStages = 8;
 constexpr int kMaxNx = 512;
 
 struct BandGeo {
@@ -46,7 +46,10 @@ struct BandGeo {
   int nbands;
   int zs, zchunk;    // z split
   int nitems;
-  int stage_bytes;
+  int p_bytes;       // p slab: NBX boxes of (RB+2) rows
+  int xr_bytes;      // x (or r) slab of the update mode: NBX boxes of RB rows
+  int stage_bytes;   // p_bytes (+ 2*xr_bytes in update mode)
+  int nstages;
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -171,16 +174,19 @@ __device__ __forceinline__ Item make_item(const RankDev& P, const BandGeo& G, in
 template <int KIND, int OUT>
 __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ RankDev P,
                                                       const __grid_constant__ CUtensorMap tmap,
+                                                      const __grid_constant__ CUtensorMap tmx,
+                                                      const __grid_constant__ CUtensorMap tmr,
                                                       const __grid_constant__ BandGeo G, double* __restrict__ out,
                                                       int mode) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ double red_smem[64];
-  __shared__ __align__(8) unsigned long long bars[2 * kStages];
+  __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
   Scalars& S = P.ctrl->s;
   if (S.done != 0) return;
-  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
+  const unsigned kStages = (unsigned)G.nstages;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kStages; ++s) {
+    for (unsigned s = 0; s < kStages; ++s) {
       mbar_init(full0 + 8 * s, 1);
       mbar_init(empty0 + 8 * s, kNC / 32);
     }
@@ -218,10 +224,18 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
           if ((q == -1 && nb_zlo) || (q == L.nz && nb_zhi)) wait_flags();
           const unsigned st = n % kStages, ph = (n / kStages) & 1u;
           mbar_wait(empty0 + 8 * st, ph ^ 1u);
-          mbar_expect_tx(full0 + 8 * st, (unsigned)G.stage_bytes);
+          const bool with_xr = OUT == 2 && s >= 2;  // this step emits a plane: bring its x and r rows too
+          mbar_expect_tx(full0 + 8 * st, (unsigned)(G.p_bytes + (with_xr ? 2 * G.xr_bytes : 0)));
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
           for (int b = 0; b < G.NBX; ++b)
             tma_load_3d(dst + b * (G.RB + 2) * BW * 8, &tmap, b * BW, y0, q + 1, full0 + 8 * st);
+          if (with_xr) {
+            const int ko = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
+            for (int b = 0; b < G.NBX; ++b) {
+              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, &tmx, b * BW, y0 + 1, ko + 1, full0 + 8 * st);
+              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, &tmr, b * BW, y0 + 1, ko + 1, full0 + 8 * st);
+            }
+          }
         }
       }
     }
@@ -232,12 +246,14 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
     const bool active = ly < G.LY && i < L.nx;
     const int ra = 2 * ly;
     Taps tp;
+    int xr_off;
     {
       const int b = i / BW, col = i % BW;
       const int boxb = (G.RB + 2) * BW * 8;
       tp.c = b * boxb + col * 8;
       tp.l = i == 0 ? -1 : (col == 0 ? (b - 1) * boxb + (BW - 1) * 8 : tp.c - 8);
       tp.r = i + 2 >= L.nx ? -1 : (col + 2 == BW ? (b + 1) * boxb : tp.c + 16);
+      xr_off = b * (G.RB * BW * 8) + (ra * BW + col) * 8;
     }
     unsigned n = 0;
     for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
@@ -250,26 +266,21 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       // index of (i, ja) on the plane emitted at step 2, then advanced by ps per step
       int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);
       PS2 pa, pb, ca, cb, na, nb;
-      double2 xa = make_double2(0, 0), xb = xa, ra2 = xa, rb2 = xa;  // x/r pairs of the next output plane
       for (int s = 0; s < nsteps; ++s, ++n) {
         const unsigned st = n % kStages, ph = (n / kStages) & 1u;
         mbar_wait(full0 + 8 * st, ph);
-        if (active) plane_from_slab<KIND>(smem_raw + (size_t)st * G.stage_bytes, tp, ra, na, nb);
+        const unsigned char* stage = smem_raw + (size_t)st * G.stage_bytes;
+        if (active) plane_from_slab<KIND>(stage, tp, ra, na, nb);
+        double2 cxa = make_double2(0, 0), cxb = cxa, cra = cxa, crb = cxa;
+        if (OUT == 2 && s >= 2 && active) {  // x and r rows of the plane emitted now (TMA-staged)
+          const unsigned char* xs = stage + G.p_bytes + xr_off;
+          cxa = *reinterpret_cast<const double2*>(xs);
+          cxb = *reinterpret_cast<const double2*>(xs + BW * 8);
+          cra = *reinterpret_cast<const double2*>(xs + G.xr_bytes);
+          crb = *reinterpret_cast<const double2*>(xs + G.xr_bytes + BW * 8);
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
-        const double2 cxa = xa, cxb = xb, cra = ra2, crb = rb2;
-        if (OUT == 2 && s >= 1 && s + 1 < nsteps) {
-          // prefetch x and r of the plane that is emitted at step s+1
-          const int64_t in = s >= 2 ? idx + ps : idx;
-          if (va) {
-            xa = *reinterpret_cast<const double2*>(P.x + in);
-            ra2 = *reinterpret_cast<const double2*>(P.r + in);
-          }
-          if (vb) {
-            xb = *reinterpret_cast<const double2*>(P.x + in + L.pitch);
-            rb2 = *reinterpret_cast<const double2*>(P.r + in + L.pitch);
-          }
-        }
         if (s >= 2) {
           if (va) emit<KIND, OUT>(P, out, pa, ca, na, idx, pair, alpha, cxa, cra, acc);
           if (vb) emit<KIND, OUT>(P, out, pb, cb, nb, idx + L.pitch, pair, alpha, cxb, crb, acc);
@@ -312,7 +323,7 @@ EncodeFn get_encode() {
   return fn;
 }
 
-bool make_geo(const RankDev& P, int nsm, BandGeo* out, int* grid, size_t* smem) {
+bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size_t* smem) {
   const cgb_layout_t& L = P.lay;
   if (!kind_is_3d(P.st.kind) || L.nx > kMaxNx) return false;
   BandGeo G{};
@@ -322,8 +333,13 @@ bool make_geo(const RankDev& P, int nsm, BandGeo* out, int* grid, size_t* smem) 
   G.RB = 2 * G.LY;
   G.NBX = (L.nx + BW - 1) / BW;
   G.nbands = (L.ny + G.RB - 1) / G.RB;
-  G.stage_bytes = G.NBX * (G.RB + 2) * BW * 8;
-  const size_t sm = (size_t)kStages * G.stage_bytes;
+  G.p_bytes = G.NBX * (G.RB + 2) * BW * 8;
+  G.xr_bytes = G.NBX * G.RB * BW * 8;
+  G.stage_bytes = G.p_bytes + (mode == kSpmvUpdate ? 2 * G.xr_bytes : 0);
+  G.nstages = (int)((200 * 1024) / G.stage_bytes);
+  if (G.nstages > (mode == kSpmvUpdate ? 4 : 6)) G.nstages = mode == kSpmvUpdate ? 4 : 6;
+  if (G.nstages < 2) return false;
+  const size_t sm = (size_t)G.nstages * G.stage_bytes;
   const int capacity = nsm;  // 544 threads x ~96 registers: one CTA per SM
   int zs = capacity / G.nbands;
   if (zs > L.nz / 8) zs = L.nz / 8;
@@ -345,10 +361,11 @@ bool spmv_tma_supported(const RankDev& P) {
   BandGeo G;
   int grid;
   size_t sm;
-  return make_geo(P, 148, &G, &grid, &sm);
+  return make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm) && make_geo(P, 148, kSpmvUpdate, &G, &grid, &sm);
 }
 
-int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out) {
+// halo_rows = 1: slabs of RB+2 rows (SpMV input); 0: exactly the band's RB rows (x / r of the update).
+int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows) {
   EncodeFn enc = get_encode();
   if (!enc) return fail(CGB_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   RankDev P{};
@@ -357,10 +374,10 @@ int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out) {
   BandGeo G;
   int grid;
   size_t sm;
-  if (!make_geo(P, 148, &G, &grid, &sm)) return fail(CGB_ERR_UNSUPPORTED, "layout not supported by the TMA SpMV");
+  if (!make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm)) return fail(CGB_ERR_UNSUPPORTED, "layout not supported by the TMA SpMV");
   cuuint64_t dims[3] = {(cuuint64_t)L.nx, (cuuint64_t)L.py, (cuuint64_t)L.pz};
   cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.pitch * L.py * 8};
-  cuuint32_t box[3] = {BW, (cuuint32_t)(G.RB + 2), 1};
+  cuuint32_t box[3] = {BW, (cuuint32_t)(G.RB + (halo_rows ? 2 : 0)), 1};
   cuuint32_t es[3] = {1, 1, 1};
   CUresult r = enc((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(vec), dims, strides,
                    box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -369,7 +386,8 @@ int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out) {
   return CGB_OK;
 }
 
-cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, double* out, int mode, cudaStream_t s) {
+cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_x, const void* map_r,
+                            double* out, int mode, cudaStream_t s) {
   static bool attr_set[64] = {};
   if (device >= 0 && device < 64 && !attr_set[device]) {
     const int lim = 220 * 1024;
@@ -388,14 +406,17 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, doubl
   BandGeo G;
   int grid;
   size_t sm;
-  if (!make_geo(P, nsm, &G, &grid, &sm)) return cudaErrorInvalidConfiguration;
+  if (!make_geo(P, nsm, mode, &G, &grid, &sm)) return cudaErrorInvalidConfiguration;
+  if (mode == kSpmvUpdate && (!map_x || !map_r)) return cudaErrorInvalidValue;
   const CUtensorMap& tm = *reinterpret_cast<const CUtensorMap*>(map);
+  const CUtensorMap& tx = *reinterpret_cast<const CUtensorMap*>(map_x ? map_x : map);
+  const CUtensorMap& tr = *reinterpret_cast<const CUtensorMap*>(map_r ? map_r : map);
   const bool k7 = P.st.kind == CGB_KIND_POISSON3D7;
   if (!k7 && P.st.kind != CGB_KIND_STENCIL3D27) return cudaErrorInvalidValue;
 #define CGB_TMA_LAUNCH(OUT)                                                                        \
   do {                                                                                             \
-    if (k7) k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, G, out, mode);        \
-    else k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, G, out, mode);          \
+    if (k7) k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, tx, tr, G, out, mode); \
+    else k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, tx, tr, G, out, mode);   \
   } while (0)
   if (mode == kSpmvUpdate) CGB_TMA_LAUNCH(2);
   else if (mode == kSpmvAlphaNoStore) CGB_TMA_LAUNCH(1);

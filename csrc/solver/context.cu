@@ -75,7 +75,9 @@ int alloc_common(cgb_ctx* c) {
   if (spmv_tma_supported(P)) {
     int r0 = spmv_tma_make_map(c->lay, P.exch[0], c->tmap[0]);
     int r1 = spmv_tma_make_map(c->lay, P.exch[1], c->tmap[1]);
-    c->tma_ok = (r0 == CGB_OK && r1 == CGB_OK);
+    int r2 = spmv_tma_make_map(c->lay, P.x, c->tmap_x, 0);
+    int r3 = spmv_tma_make_map(c->lay, P.r, c->tmap_r, 0);
+    c->tma_ok = (r0 == CGB_OK && r1 == CGB_OK && r2 == CGB_OK && r3 == CGB_OK);
   }
   // timeout for peer waits lives in the control block and survives solves
   Scalars init{};
@@ -391,7 +393,7 @@ static bool use_tma(const cgb_ctx* c) {
 static int enqueue_spmv(cgb_ctx* c, int buf, int mode, cudaStream_t s) {
   const RankDev& P = c->P;
   if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[buf], P.Ap, mode, s));
-  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[buf], P.Ap, mode, s));
+  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[buf], nullptr, nullptr, P.Ap, mode, s));
   else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[buf], P.Ap, mode, s));
   return CGB_OK;
 }
@@ -407,8 +409,8 @@ int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
   double* p = P.exch[0];
   if (c->opts.variant == CGB_VAR_MERGED) {
     // 72 B/DOF: Ap is never stored; the update kernel re-evaluates the stencil from the p slabs
-    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvAlphaNoStore, s));
-    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.Ap, kSpmvUpdate, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], nullptr, nullptr, P.Ap, kSpmvAlphaNoStore, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_x, c->tmap_r, P.Ap, kSpmvUpdate, s));
     CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));
     return CGB_OK;
   }
@@ -501,7 +503,7 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
     // w0 = A r0 (r0 = b sits in exchange buffer 0 after k_init), then the first (gamma, delta)
     const RankDev& P = c->P;
     if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.exch[1], kSpmvPlain, c->stream));
-    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], P.exch[1], kSpmvPlain, c->stream));
+    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], nullptr, nullptr, P.exch[1], kSpmvPlain, c->stream));
     else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.exch[1], kSpmvPlain, c->stream));
     CGB_CUDA(launch_pipe_start(P, c->cfg, 1, c->stream));
     c->launches += 2;

@@ -51,6 +51,8 @@ struct cgb_ctx {
   long long launches_at_begin = 0;
   std::map<long long, cudaGraphExec_t> graphs;  // key: variant/impl/length
   alignas(64) unsigned char tmap[2][128] = {};  // CUtensorMap of exch[0], exch[1] (spmv_tma.cu)
+  alignas(64) unsigned char tmap_x[128] = {};   // band-row maps of x and r (update mode)
+  alignas(64) unsigned char tmap_r[128] = {};
   bool tma_ok = false;
 
   ~cgb_ctx();
