@@ -6,6 +6,8 @@
 // of the device convergence flag every `chunk` iterations, one chunk behind the GPU.
 #include "context.hpp"
 
+#include <nvtx3/nvToolsExt.h>  // header-only; ranges show up in Nsight timelines
+
 #include <algorithm>
 #include <climits>
 #include <cstdlib>
@@ -25,6 +27,11 @@ long long default_timeout_cycles() {
   return (long long)(ms * 2.0e6);
 }
 #define kDefaultTimeoutCycles default_timeout_cycles()
+
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
@@ -458,6 +465,7 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
 // others, and those would already be spinning on this rank's first message.
 extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c && o, "cgb_solve_prepare: NULL argument");
+  NvtxRange nvtx_("cgb.solve_prepare");
   CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_AUTO, "unknown variant %d", o->variant);
   if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
     return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
@@ -493,6 +501,7 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
 
 extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c && o, "cgb_solve_begin: NULL argument");
+  NvtxRange nvtx_("cgb.solve_begin");
   CGB_TRY(cgb_solve_prepare(c, o));
   c->launches_at_begin = c->launches;
   CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit, c->stream));
@@ -518,6 +527,7 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
 
 extern "C" int cgb_solve_iterate(cgb_ctx* c, int n) {
   CGB_REQUIRE(c, "cgb_solve_iterate: NULL context");
+  NvtxRange nvtx_("cgb.solve_iterate");
   if (!c->active) return fail(CGB_ERR_STATE, "cgb_solve_iterate before cgb_solve_begin");
   CGB_CUDA(cudaSetDevice(c->device));
   const int chunk = c->opts.chunk;
@@ -584,6 +594,7 @@ extern "C" int cgb_solve_poll(cgb_ctx* c, int wait, cgb_solve_result_t* res) {
 
 extern "C" int cgb_solve_finish(cgb_ctx* c, cgb_solve_result_t* res) {
   CGB_REQUIRE(c, "cgb_solve_finish: NULL context");
+  NvtxRange nvtx_("cgb.solve_finish");
   if (!c->active) return fail(CGB_ERR_STATE, "cgb_solve_finish before cgb_solve_begin");
   CGB_CUDA(cudaSetDevice(c->device));
   CGB_CUDA(cudaEventRecord(c->ev_end, c->stream));
