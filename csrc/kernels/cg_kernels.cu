@@ -61,7 +61,7 @@ __device__ __forceinline__ void push_pair(const RankDev& P, int exch_buf, unsign
 // rho = b.b (CUDACG.cu:261-266 without the sqrt/square round trip), halo push of p0.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankDev P, double tol, int tol_mode,
-                                                    int maxit) {
+                                                    int maxit, int bump_halo) {
   __shared__ double red_smem[64];
   __shared__ unsigned cnt[CGB_NDIR];
   Scalars& S = P.ctrl->s;
@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
       S.pending_x = 0;
       S.alpha = 0.0;
       S.beta = 0.0;
-      S.halo_seq = version;
+      S.halo_seq = version + (bump_halo ? 1 : 0);
       S.done = !ok ? (int)CGB_ERR_TIMEOUT : (isfinite(a) && a > 0.0 ? 0 : (a == 0.0 ? 1 : (int)CGB_ERR_BREAKDOWN));
     }
   }
@@ -496,8 +496,9 @@ void choose_spmv_tiling(RankDev& P, int grid_spmv) {
   }
 }
 
-cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit, cudaStream_t s) {
-  k_init<<<c.grid_ew, kThreads, 0, s>>>(P, tol, tol_mode, maxit);
+cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit, int bump_halo,
+                        cudaStream_t s) {
+  k_init<<<c.grid_ew, kThreads, 0, s>>>(P, tol, tol_mode, maxit, bump_halo);
   return cudaGetLastError();
 }
 

@@ -10,7 +10,8 @@ enum SpmvMode {
   kSpmvPlain = 2,  // no reduction at all
   // TMA kernel only ("recompute" variant): trade a second stencil evaluation for 16 B/DOF
   kSpmvAlphaNoStore = 3,  // like kSpmvAlpha but Ap is never written
-  kSpmvUpdate = 4         // recompute Ap from p; x += alpha p; r -= alpha Ap; r.r -> test, beta
+  kSpmvUpdate = 4,        // recompute Ap from p; x += alpha p; r -= alpha Ap; r.r -> test, beta
+  kSpmvPUpdate = 5        // (k_pspmv_tma) p_new = r + beta p_old folded into the SpMV, p.Ap -> alpha
 };
 
 struct LaunchCfg {
@@ -25,7 +26,9 @@ int query_launch_cfg(int device, LaunchCfg* cfg);
 void choose_spmv_tiling(RankDev& P, int grid_spmv);
 
 // r = b, p = b, x = 0, push p's boundary rows, rho = all-reduce(b.b), thresh, iter = 0.
-cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit,
+// bump_halo: the next kernel that pushes halos is not preceded by an x/r update (merged variant), so
+// the version it will publish is announced here.
+cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit, int bump_halo,
                         cudaStream_t s);
 // out = A in (+ reduction according to mode); simple = register-marching kernel.
 cudaError_t launch_spmv_simple(const RankDev& P, const LaunchCfg& c, const double* in, double* out,
@@ -36,6 +39,9 @@ int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, i
 // map_x / map_r (halo_rows = 0 maps of x and r) are needed for mode kSpmvUpdate only.
 cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_x, const void* map_r,
                             double* out, int mode, cudaStream_t s);
+// "merged" variant: p-update folded into the SpMV (maps: r with halo rows, p_old, p_new buffers).
+cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* map_r, const void* map_pold,
+                             const void* map_pnew, const double* pold, double* pnew, int newbuf, cudaStream_t s);
 cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* in, double* out, int mode,
                             cudaStream_t s);
 // x += alpha p; r -= alpha Ap; rho' = all-reduce(r.r); convergence test; beta.

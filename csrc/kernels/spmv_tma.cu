@@ -306,6 +306,177 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// k_pspmv_tma ("merged" variant, 64 B/DOF): the p-update is folded into the SpMV.
+//   p_new = r + beta * p_old   on the band's RB+2 rows of every plane (computed in shared memory
+//                              from TMA slabs of r and p_old: the two halo rows are RECOMPUTED
+//                              instead of waiting for the neighbouring band),
+//   p_new -> global (owned rows only, into the other exchange buffer), p_new.A p_new -> alpha.
+// Boundary first: before the sweep all threads compute p_new on the rank's first/last plane and
+// store it straight into the neighbours' ghost planes (P2P) and raise their flags; the sweep runs
+// towards the ghost plane, so the neighbour's data is needed last. For a ghost plane the "r slab"
+// is loaded from the neighbour-written ghost plane of the NEW buffer and used as is.
+// Replaces cublasDscal + cublasDaxpy + cusparseSpMV + cublasDdot (CUDACG.cu:342-347, 288-304).
+// z-slab decompositions only (no y neighbours).
+// ---------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ RankDev P,
+                                                       const __grid_constant__ CUtensorMap tm_r,
+                                                       const __grid_constant__ CUtensorMap tm_pold,
+                                                       const __grid_constant__ CUtensorMap tm_pnew,
+                                                       const __grid_constant__ BandGeo G,
+                                                       const double* __restrict__ pold, double* __restrict__ pnew,
+                                                       int newbuf) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ double red_smem[64];
+  __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
+  __shared__ unsigned cnt[CGB_NDIR];
+  Scalars& S = P.ctrl->s;
+  if (S.done != 0) return;
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
+  const unsigned kStages = (unsigned)G.nstages;
+  if (threadIdx.x == 0) {
+    for (unsigned s = 0; s < kStages; ++s) {
+      mbar_init(full0 + 8 * s, 1);
+      mbar_init(empty0 + 8 * s, kNC / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
+  __syncthreads();
+
+  const cgb_layout_t& L = P.lay;
+  const double beta = S.beta;
+  const u64 version = S.halo_seq;
+  const bool nb_zlo = P.nbr[dir_index(0, -1)] >= 0, nb_zhi = P.nbr[dir_index(0, 1)] >= 0;
+
+  // ---- boundary planes first: push p_new of my first/last plane into the neighbours' ghosts ----
+  if (P.nbr_mask) {
+    const unsigned pw = (unsigned)((L.nx + 1) / 2);
+    const unsigned per_plane = (unsigned)L.ny * pw;
+    const unsigned total = ((nb_zlo ? 1u : 0u) + (nb_zhi ? 1u : 0u)) * per_plane;
+    for (unsigned u = blockIdx.x * kNT + threadIdx.x; u < total; u += gridDim.x * kNT) {
+      const unsigned pl = u / per_plane, v = u - pl * per_plane;
+      const int j = (int)(v / pw), i = 2 * (int)(v - (unsigned)j * pw);
+      const bool lo = pl == 0 && nb_zlo;
+      const int k = lo ? 0 : L.nz - 1;
+      const int d = lo ? dir_index(0, -1) : dir_index(0, 1);
+      const int64_t idx = lay_index(L, i, j, k);
+      const double2 vr = *reinterpret_cast<const double2*>(P.r + idx);
+      double2 vp = *reinterpret_cast<const double2*>(pold + idx);
+      vp.x = vr.x + beta * vp.x;
+      vp.y = vr.y + beta * vp.y;
+      *reinterpret_cast<double2*>(P.nbr_exch[newbuf][d] + ghost_index(P, d, i, j, k)) = vp;
+      atomicAdd(&cnt[d], 1u);
+    }
+    halo_commit(P, cnt, version);
+  }
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int boxb = (G.RB + 2) * BW * 8;
+  double acc = 0.0;
+
+  if (warp == kNC / 32) {
+    if (lane == 0) {
+      unsigned n = 0;
+      bool waited = false;
+      for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
+        const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
+        const int y0 = it.band * G.RB;
+        const int nsteps = it.k1 - it.k0 + 2;
+        for (int s = 0; s < nsteps; ++s, ++n) {
+          const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
+          const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
+          if (ghost && !waited) {
+            for (int d = 0; d < CGB_NDIR; ++d)
+              if (d != 4 && P.nbr[d] >= 0 && !spin_until_ge(&P.ctrl->halo_flag[d], version, S.timeout_cycles))
+                S.done = CGB_ERR_TIMEOUT;
+            asm volatile("fence.proxy.async;" ::: "memory");
+            waited = true;
+          }
+          const unsigned st = n % kStages, ph = (n / kStages) & 1u;
+          mbar_wait(empty0 + 8 * st, ph ^ 1u);
+          mbar_expect_tx(full0 + 8 * st, (unsigned)(2 * G.p_bytes));
+          const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
+          for (int b = 0; b < G.NBX; ++b) {
+            tma_load_3d(dst + b * boxb, ghost ? &tm_pnew : &tm_r, b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + b * boxb, &tm_pold, b * BW, y0, q + 1, full0 + 8 * st);
+          }
+        }
+      }
+    }
+  } else {
+    const int lx = threadIdx.x % G.LX, ly = threadIdx.x / G.LX;
+    const int i = 2 * lx;
+    const bool active = ly < G.LY && i < L.nx;
+    const int ra = 2 * ly;
+    const int bx = i / BW, col = i % BW;
+    Taps tp;
+    tp.c = bx * boxb + col * 8;
+    tp.l = i == 0 ? -1 : (col == 0 ? (bx - 1) * boxb + (BW - 1) * 8 : tp.c - 8);
+    tp.r = i + 2 >= L.nx ? -1 : (col + 2 == BW ? (bx + 1) * boxb : tp.c + 16);
+    const bool pair = i + 1 < L.nx;
+    unsigned n = 0;
+    for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
+      const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
+      const int j0 = it.band * G.RB;
+      const int ja = j0 + ra;
+      const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
+      const bool va = ja < jend, vb = ja + 1 < jend;
+      const int nsteps = it.k1 - it.k0 + 2;
+      const int64_t ps = (int64_t)L.pitch * L.py * it.dir;
+      int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);
+      PS2 pa, pb, ca, cb, na, nb;
+      for (int s = 0; s < nsteps; ++s, ++n) {
+        const unsigned st = n % kStages, ph = (n / kStages) & 1u;
+        const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
+        const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
+        const bool inb = q >= 0 && q < L.nz;
+        mbar_wait(full0 + 8 * st, ph);
+        unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
+        unsigned char* pslab = rs + G.p_bytes;
+        if (active) {
+          for (int row = ly; row < G.RB + 2; row += G.LY) {  // p_new on my share of the slab rows
+            const int off = bx * boxb + (row * BW + col) * 8;
+            const double2 vr = *reinterpret_cast<const double2*>(rs + off);
+            const double2 vp = *reinterpret_cast<const double2*>(pslab + off);
+            double2 vn;
+            vn.x = ghost ? vr.x : vr.x + beta * vp.x;
+            vn.y = ghost ? vr.y : vr.y + beta * vp.y;
+            *reinterpret_cast<double2*>(pslab + off) = vn;
+            const int j = j0 + row - 1;
+            if (inb && row >= 1 && row <= G.RB && j < L.ny) {
+              const int64_t o = lay_index(L, i, j, q);
+              if (pair) *reinterpret_cast<double2*>(pnew + o) = vn;
+              else pnew[o] = vn.x;
+            }
+          }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(kNC) : "memory");  // slab of p_new complete (consumers only)
+        if (active) plane_from_slab<KIND>(pslab, tp, ra, na, nb);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty0 + 8 * st);
+        if (s >= 2) {
+          const double2 z2 = make_double2(0, 0);
+          if (va) emit<KIND, 1>(P, nullptr, pa, ca, na, idx, pair, 0.0, z2, z2, acc);
+          if (vb) emit<KIND, 1>(P, nullptr, pb, cb, nb, idx + L.pitch, pair, 0.0, z2, z2, acc);
+          idx += ps;
+        }
+        pa = ca; pb = cb;
+        ca = na; cb = nb;
+      }
+    }
+  }
+  double a = acc, z = 0.0;
+  if (grid_sum2_last_t<kNT>(a, z, P.partials, &S.ticket_red, red_smem)) {
+    allreduce2_last_cta(P, a, z, red_smem);
+    if (threadIdx.x == 0) {
+      S.pAp = a;
+      S.alpha = S.rho / a;
+    }
+  }
+}
+
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -335,9 +506,10 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
   G.nbands = (L.ny + G.RB - 1) / G.RB;
   G.p_bytes = G.NBX * (G.RB + 2) * BW * 8;
   G.xr_bytes = G.NBX * G.RB * BW * 8;
-  G.stage_bytes = G.p_bytes + (mode == kSpmvUpdate ? 2 * G.xr_bytes : 0);
+  G.stage_bytes = mode == kSpmvPUpdate ? 2 * G.p_bytes : G.p_bytes + (mode == kSpmvUpdate ? 2 * G.xr_bytes : 0);
   G.nstages = (int)((200 * 1024) / G.stage_bytes);
-  if (G.nstages > (mode == kSpmvUpdate ? 4 : 6)) G.nstages = mode == kSpmvUpdate ? 4 : 6;
+  const int cap = mode == kSpmvAlpha || mode == kSpmvDot || mode == kSpmvPlain || mode == kSpmvAlphaNoStore ? 6 : 4;
+  if (G.nstages > cap) G.nstages = cap;
   if (G.nstages < 2) return false;
   const size_t sm = (size_t)G.nstages * G.stage_bytes;
   const int capacity = nsm;  // 544 threads x ~96 registers: one CTA per SM
@@ -361,7 +533,8 @@ bool spmv_tma_supported(const RankDev& P) {
   BandGeo G;
   int grid;
   size_t sm;
-  return make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm) && make_geo(P, 148, kSpmvUpdate, &G, &grid, &sm);
+  return make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm) && make_geo(P, 148, kSpmvUpdate, &G, &grid, &sm) &&
+         make_geo(P, 148, kSpmvPUpdate, &G, &grid, &sm);
 }
 
 // halo_rows = 1: slabs of RB+2 rows (SpMV input); 0: exactly the band's RB rows (x / r of the update).
@@ -422,6 +595,34 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
   else if (mode == kSpmvAlphaNoStore) CGB_TMA_LAUNCH(1);
   else CGB_TMA_LAUNCH(0);
 #undef CGB_TMA_LAUNCH
+  return cudaGetLastError();
+}
+
+cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* map_r, const void* map_pold,
+                             const void* map_pnew, const double* pold, double* pnew, int newbuf, cudaStream_t s) {
+  static bool attr_set[64] = {};
+  if (device >= 0 && device < 64 && !attr_set[device]) {
+    const auto at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    cudaError_t e = cudaFuncSetAttribute(k_pspmv_tma<CGB_KIND_POISSON3D7>, at, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pspmv_tma<CGB_KIND_STENCIL3D27>, at, 220 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_set[device] = true;
+  }
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device);
+  BandGeo G;
+  int grid;
+  size_t sm;
+  if (!make_geo(P, nsm, kSpmvPUpdate, &G, &grid, &sm)) return cudaErrorInvalidConfiguration;
+  const CUtensorMap& tr = *reinterpret_cast<const CUtensorMap*>(map_r);
+  const CUtensorMap& to = *reinterpret_cast<const CUtensorMap*>(map_pold);
+  const CUtensorMap& tn = *reinterpret_cast<const CUtensorMap*>(map_pnew);
+  if (P.st.kind == CGB_KIND_POISSON3D7)
+    k_pspmv_tma<CGB_KIND_POISSON3D7><<<grid, kNT, sm, s>>>(P, tr, to, tn, G, pold, pnew, newbuf);
+  else if (P.st.kind == CGB_KIND_STENCIL3D27)
+    k_pspmv_tma<CGB_KIND_STENCIL3D27><<<grid, kNT, sm, s>>>(P, tr, to, tn, G, pold, pnew, newbuf);
+  else
+    return cudaErrorInvalidValue;
   return cudaGetLastError();
 }
 

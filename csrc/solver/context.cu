@@ -84,7 +84,8 @@ int alloc_common(cgb_ctx* c) {
     int r1 = spmv_tma_make_map(c->lay, P.exch[1], c->tmap[1]);
     int r2 = spmv_tma_make_map(c->lay, P.x, c->tmap_x, 0);
     int r3 = spmv_tma_make_map(c->lay, P.r, c->tmap_r, 0);
-    c->tma_ok = (r0 == CGB_OK && r1 == CGB_OK && r2 == CGB_OK && r3 == CGB_OK);
+    int r4 = spmv_tma_make_map(c->lay, P.r, c->tmap_rh, 1);
+    c->tma_ok = (r0 == CGB_OK && r1 == CGB_OK && r2 == CGB_OK && r3 == CGB_OK && r4 == CGB_OK);
   }
   // timeout for peer waits lives in the control block and survives solves
   Scalars init{};
@@ -380,11 +381,18 @@ extern "C" void cgb_solve_opts_default(cgb_solve_opts_t* o) {
 
 namespace cgb {
 
+// variants whose SpMV input ping-pongs between the two exchange buffers
+static bool uses_parity(const cgb_ctx* c) {
+  return c->opts.variant == CGB_VAR_PIPELINED || c->opts.variant == CGB_VAR_MERGED2;
+}
+static bool merged2_ok(const cgb_ctx* c) { return c->tma_ok && c->part.Py == 1; }
+
 // kernels per iteration of a variant (for the launch counter)
 static int launches_per_iter(const cgb_ctx* c) {
   switch (c->opts.variant) {
     case CGB_VAR_FUSED: return 3;
     case CGB_VAR_PIPELINED: return 2;
+    case CGB_VAR_MERGED2: return 2;
     default: return 3;
   }
 }
@@ -411,6 +419,14 @@ int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
     CGB_TRY(enqueue_spmv(c, c->host_cur, kSpmvPlain, s));            // q = A w
     CGB_CUDA(launch_pipe_update(P, c->cfg, c->host_cur, s));         // consumes (gamma,delta), publishes the next
     c->host_cur ^= 1;
+    return CGB_OK;
+  }
+  if (c->opts.variant == CGB_VAR_MERGED2) {
+    // 64 B/DOF, two kernels: (p-update + SpMV + p.Ap) then (stencil again + x/r update + r.r)
+    const int cur = c->host_cur, nb = cur ^ 1;
+    CGB_CUDA(launch_pspmv_tma(P, c->device, c->tmap_rh, c->tmap[cur], c->tmap[nb], P.exch[cur], P.exch[nb], nb, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[nb], c->tmap_x, c->tmap_r, P.Ap, kSpmvUpdate, s));
+    c->host_cur = nb;
     return CGB_OK;
   }
   double* p = P.exch[0];
@@ -466,9 +482,11 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
 extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c && o, "cgb_solve_prepare: NULL argument");
   NvtxRange nvtx_("cgb.solve_prepare");
-  CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_AUTO, "unknown variant %d", o->variant);
+  CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_MERGED2, "unknown variant %d", o->variant);
   if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
     return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
+  if (o->variant == CGB_VAR_MERGED2 && !merged2_ok(c))
+    return fail(CGB_ERR_UNSUPPORTED, "the merged variant needs the TMA SpMV (3D stencil, nx <= 512) and a z-slab decomposition");
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
   if (c->opts.variant == CGB_VAR_AUTO)
@@ -490,7 +508,7 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   if (c->opts.use_graph) {
     cudaGraphExec_t ge;
     const int saved = c->host_cur;
-    for (int par = 0; par < (c->opts.variant == CGB_VAR_PIPELINED ? 2 : 1); ++par) {
+    for (int par = 0; par < (uses_parity(c) ? 2 : 1); ++par) {
       c->host_cur = par;
       CGB_TRY(get_graph(c, c->opts.chunk, &ge));
     }
@@ -504,7 +522,8 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   NvtxRange nvtx_("cgb.solve_begin");
   CGB_TRY(cgb_solve_prepare(c, o));
   c->launches_at_begin = c->launches;
-  CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit, c->stream));
+  CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit,
+                       c->opts.variant == CGB_VAR_MERGED2 ? 1 : 0, c->stream));
   c->launches += 1;
   c->host_cur = 0;
   c->iters_target = c->opts.maxit;
@@ -536,7 +555,7 @@ extern "C" int cgb_solve_iterate(cgb_ctx* c, int n) {
       cudaGraphExec_t ge;
       CGB_TRY(get_graph(c, chunk, &ge));
       CGB_CUDA(cudaGraphLaunch(ge, c->stream));
-      if (c->opts.variant == CGB_VAR_PIPELINED) c->host_cur ^= (chunk & 1);
+      if (uses_parity(c)) c->host_cur ^= (chunk & 1);
       n -= chunk;
       c->enqueued += chunk;
       c->launches += (long long)chunk * launches_per_iter(c);

@@ -53,6 +53,7 @@ struct cgb_ctx {
   alignas(64) unsigned char tmap[2][128] = {};  // CUtensorMap of exch[0], exch[1] (spmv_tma.cu)
   alignas(64) unsigned char tmap_x[128] = {};   // band-row maps of x and r (update mode)
   alignas(64) unsigned char tmap_r[128] = {};
+  alignas(64) unsigned char tmap_rh[128] = {};  // r with halo rows (merged variant)
   bool tma_ok = false;
 
   ~cgb_ctx();

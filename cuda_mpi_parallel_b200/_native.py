@@ -19,7 +19,7 @@ IPC_HANDLE_BYTES = 64
 KIND_CSR, KIND_POISSON2D5, KIND_POISSON3D7, KIND_STENCIL3D27 = 0, 1, 2, 3
 RHS_ONES, RHS_RANDOM, RHS_MANUFACTURED = 0, 1, 2
 TOL_ABS, TOL_REL = 0, 1
-VAR_FUSED, VAR_MERGED, VAR_PIPELINED, VAR_AUTO = 0, 1, 2, 3
+VAR_FUSED, VAR_MERGED, VAR_PIPELINED, VAR_AUTO, VAR_MERGED2 = 0, 1, 2, 3, 4
 SPMV_AUTO, SPMV_SIMPLE, SPMV_TMA = 0, 1, 2
 
 STATUS_NAMES = {0: "ok", -1: "invalid argument", -2: "CUDA error", -3: "bad state", -4: "peer wait timeout",

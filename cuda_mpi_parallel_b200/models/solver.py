@@ -25,7 +25,7 @@ from .. import _native as N
 from ..parallel.partition import make_layout, make_partition
 from .problems import Problem, _RHS
 
-_VARIANTS = {"auto": N.VAR_AUTO, "fused": N.VAR_FUSED, "recompute": N.VAR_MERGED, "merged": N.VAR_MERGED, "pipelined": N.VAR_PIPELINED}
+_VARIANTS = {"auto": N.VAR_AUTO, "fused": N.VAR_FUSED, "recompute": N.VAR_MERGED, "merged": N.VAR_MERGED2, "pipelined": N.VAR_PIPELINED}
 _SPMV = {"auto": N.SPMV_AUTO, "simple": N.SPMV_SIMPLE, "tma": N.SPMV_TMA}
 
 

@@ -147,7 +147,10 @@ typedef enum cgb_variant {
   CGB_VAR_MERGED = 1,     /* classic CG "recompute": Ap is never stored, the x/r update re-evaluates the
                              stencil from TMA slabs of p (72 instead of 88 B/DOF); 3D stencils, nx <= 512 */
   CGB_VAR_PIPELINED = 2,  /* Ghysels-Vanroose, one fused 2-scalar reduction per iteration */
-  CGB_VAR_AUTO = 3        /* MERGED where it applies and is measured faster (7-point 3D), else FUSED */
+  CGB_VAR_AUTO = 3,       /* fastest measured variant that applies: MERGED2, else MERGED, else FUSED */
+  CGB_VAR_MERGED2 = 4     /* classic CG, 2 kernels/iter, 64 B/DOF: p = r + beta p folded into the SpMV (halo rows
+                             recomputed in shared memory, boundary planes pushed first) + the MERGED update
+                             kernel; 3D stencils, nx <= 512, z-slab decomposition */
 } cgb_variant;
 
 typedef enum cgb_spmv_impl {

@@ -140,3 +140,23 @@ def test_recompute_variant_rejects_unsupported_shapes():
     s.set_rhs("ones")
     with pytest.raises(NativeError):
         s.solve(variant="recompute")
+
+
+@pytest.mark.parametrize("prob", [Problem.poisson3d(40, 36, 44), Problem.poisson3d(130, 37, 21), Problem.stencil27(24, 28, 24),
+                                  Problem.poisson3d(512, 24, 20), Problem.poisson3d(384, 20, 9), Problem.poisson3d(33, 5, 3)],
+                         ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
+def test_merged_variant_matches_oracle(prob):
+    # 64 B/DOF variant: p-update folded into the SpMV (halo rows recomputed in shared memory).
+    b = prob.rhs("random", seed=19)
+    ref = cpu_cg(prob, b, tol=1e-8)
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-8, variant="merged", chunk=5)
+    assert res.status == 1 and abs(res.iters - ref.iters) <= 1
+    n = min(res.iters, ref.iters)
+    h = s.history(n)
+    big = ref.history[:n] > 1e-6 * ref.r0norm
+    np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-8)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
+    r2 = s.solve(tol=1e-8, variant="merged", chunk=4, use_graph=False)     # repeat on the same context
+    assert r2.iters == res.iters and (s.history(n) == h).all()

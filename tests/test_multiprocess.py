@@ -73,3 +73,15 @@ def test_gpu_fabric_recompute_variant(name, dims, decomp):
     nproc = 2 if n < 4 else 4
     res = _run(nproc, ["gpu", name, dims, str(decomp), "recompute"], port=29740 + decomp, timeout=240)
     assert res["ok"] and res["ranks_identical"], res
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("name,dims", [("poisson3d7", "64x48x40"), ("stencil3d27", "36x42x38"), ("poisson3d7", "512x20x9")])
+def test_gpu_fabric_merged_variant(name, dims):
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nproc = 2 if n < 4 else 4
+    res = _run(nproc, ["gpu", name, dims, "1", "merged"], port=29760, timeout=240)
+    assert res["ok"] and res["ranks_identical"], res

@@ -7,7 +7,7 @@
 //
 // Everything the reference hard-codes is a flag here:
 //   --problem ref3x3|poisson2d5|poisson3d7|stencil3d27|csr:<file.mtx>     --n NX[,NY[,NZ]]
-//   --gpus P  --decomp 1d|2d[:PYxPZ]   --variant auto|fused|recompute|pipelined|cpu   --spmv auto|simple|tma
+//   --gpus P  --decomp 1d|2d[:PYxPZ]   --variant auto|fused|recompute|merged|pipelined|cpu   --spmv auto|simple|tma
 //   --tol T  --tol-mode abs|rel  --maxit N  --rhs ones|random[:seed]|manufactured
 //   --print-x / --no-print-x   --x-out FILE   --hist-out FILE   --json-out FILE   --chunk N
 // stdout stays diffable against the reference; history ("iter ||r||" as "%d %.17e") and the timing
@@ -91,7 +91,7 @@ Args parse(int argc, char** argv) {
     else if (f == "--json-out") a.json_out = need(i);
     else if (f == "--help" || f == "-h") {
       std::printf("usage: cgb200 [--problem ref3x3|poisson2d5|poisson3d7|stencil3d27|csr:<file.mtx>] [--n NX[,NY[,NZ]]]\n"
-                  "              [--gpus P] [--decomp 1d|2d[:PYxPZ]] [--variant auto|fused|recompute|pipelined|cpu] [--spmv auto|simple|tma]\n"
+                  "              [--gpus P] [--decomp 1d|2d[:PYxPZ]] [--variant auto|fused|recompute|merged|pipelined|cpu] [--spmv auto|simple|tma]\n"
                   "              [--tol T] [--tol-mode abs|rel] [--maxit N] [--rhs ones|random[:seed]|manufactured]\n"
                   "              [--print-x|--no-print-x] [--x-out F] [--hist-out F] [--json-out F] [--chunk N]\n");
       std::exit(0);
@@ -241,7 +241,8 @@ int main(int argc, char** argv) {
       o.chunk = a.chunk;
       o.variant = a.variant == "pipelined" ? CGB_VAR_PIPELINED
                 : a.variant == "fused" ? CGB_VAR_FUSED
-                : a.variant == "recompute" ? CGB_VAR_MERGED : CGB_VAR_AUTO;
+                : a.variant == "recompute" ? CGB_VAR_MERGED
+                : a.variant == "merged" ? CGB_VAR_MERGED2 : CGB_VAR_AUTO;
       o.spmv_impl = a.spmv == "simple" ? CGB_SPMV_SIMPLE : a.spmv == "tma" ? CGB_SPMV_TMA : CGB_SPMV_AUTO;
       if (P == 1) {
         check(cgb_solve(ctx[0], &o, &res), "solve");
