@@ -489,9 +489,11 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
     return fail(CGB_ERR_UNSUPPORTED, "the merged variant needs the TMA SpMV (3D stencil, nx <= 512) and a z-slab decomposition");
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
-  if (c->opts.variant == CGB_VAR_AUTO)
-    c->opts.variant = (c->tma_ok && c->st.kind == CGB_KIND_POISSON3D7 && o->spmv_impl != CGB_SPMV_SIMPLE) ? CGB_VAR_MERGED
-                                                                                                        : CGB_VAR_FUSED;
+  if (c->opts.variant == CGB_VAR_AUTO) {
+    // measured on B200 (profiles/): for the 7-point stencil merged > recompute > fused; 27-point stays fused
+    const bool tma7 = c->tma_ok && c->st.kind == CGB_KIND_POISSON3D7 && o->spmv_impl != CGB_SPMV_SIMPLE;
+    c->opts.variant = !tma7 ? CGB_VAR_FUSED : (merged2_ok(c) ? CGB_VAR_MERGED2 : CGB_VAR_MERGED);
+  }
   if (c->opts.chunk < 1) c->opts.chunk = 25;
   if (c->opts.fixed_iters > 0) {
     c->opts.maxit = c->opts.fixed_iters;
