@@ -117,6 +117,53 @@ __device__ __forceinline__ void plane_from_slab(const unsigned char* slab, const
   }
 }
 
+// Merged variant: plane sums of p_new = r + beta*p_old evaluated on the fly from the r slab and
+// the p_old slab (for a neighbour's ghost plane the "r slab" already holds p_new). Everything a
+// thread needs — its 2x2 cells, the rows above/below and the x neighbours — is recomputed in
+// registers, so no p_new slab has to be written back to shared memory and no CTA barrier is
+// needed between the update and the stencil. Also returns the thread's own p_new pairs.
+template <int KIND>
+__device__ __forceinline__ void plane_from_two(const unsigned char* rslab, const unsigned char* pslab, const Taps& tp,
+                                               int ra, double beta, bool ghost, PS2& A, PS2& B, double2& pna,
+                                               double2& pnb) {
+  constexpr int RS = BW * 8;
+  const unsigned char* r0 = rslab + ra * RS;
+  const unsigned char* p0 = pslab + ra * RS;
+  const double bt = ghost ? 0.0 : beta;  // p_old slab holds finite data (zeros or a previous p), so 0*p is exact
+  auto pn2 = [&](int row) {
+    const double2 vr = *reinterpret_cast<const double2*>(r0 + row * RS + tp.c);
+    const double2 vp = *reinterpret_cast<const double2*>(p0 + row * RS + tp.c);
+    return make_double2(vr.x + bt * vp.x, vr.y + bt * vp.y);
+  };
+  auto pnl = [&](int row) {
+    return tp.l >= 0 ? *reinterpret_cast<const double*>(r0 + row * RS + tp.l) +
+                           bt * *reinterpret_cast<const double*>(p0 + row * RS + tp.l)
+                     : 0.0;
+  };
+  auto pnr = [&](int row) {
+    return tp.r >= 0 ? *reinterpret_cast<const double*>(r0 + row * RS + tp.r) +
+                           bt * *reinterpret_cast<const double*>(p0 + row * RS + tp.r)
+                     : 0.0;
+  };
+  const double2 c0 = pn2(0), c1 = pn2(1), c2 = pn2(2), c3 = pn2(3);
+  const double l1 = pnl(1), q1 = pnr(1), l2 = pnl(2), q2 = pnr(2);
+  pna = c1;
+  pnb = c2;
+  A.s0[0] = c1.x; A.s0[1] = c1.y;
+  B.s0[0] = c2.x; B.s0[1] = c2.y;
+  A.s1[0] = (l1 + c1.y) + (c0.x + c2.x);
+  A.s1[1] = (c1.x + q1) + (c0.y + c2.y);
+  B.s1[0] = (l2 + c2.y) + (c1.x + c3.x);
+  B.s1[1] = (c2.x + q2) + (c1.y + c3.y);
+  if (KIND == CGB_KIND_STENCIL3D27) {
+    const double l0 = pnl(0), q0 = pnr(0), l3 = pnl(3), q3 = pnr(3);
+    A.s2[0] = (l0 + c0.y) + (l2 + c2.y);
+    A.s2[1] = (c0.x + q0) + (c2.x + q2);
+    B.s2[0] = (l1 + c1.y) + (l3 + c3.y);
+    B.s2[1] = (c1.x + q1) + (c3.x + q3);
+  }
+}
+
 // OUT: 0 store Ap and accumulate p.Ap; 1 accumulate p.Ap only; 2 x += alpha p, r -= alpha Ap,
 // accumulate r.r (x/r pairs were prefetched one plane ahead into vx/vr).
 template <int KIND, int OUT>
@@ -308,9 +355,9 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
 
 // ---------------------------------------------------------------------------------------------
 // k_pspmv_tma ("merged" variant, 64 B/DOF): the p-update is folded into the SpMV.
-//   p_new = r + beta * p_old   on the band's RB+2 rows of every plane (computed in shared memory
-//                              from TMA slabs of r and p_old: the two halo rows are RECOMPUTED
-//                              instead of waiting for the neighbouring band),
+//   p_new = r + beta * p_old   on the band's RB+2 rows of every plane, evaluated in registers from
+//                              TMA slabs of r and p_old: the halo rows and x neighbours are
+//                              RECOMPUTED instead of waiting for the neighbouring band/thread,
 //   p_new -> global (owned rows only, into the other exchange buffer), p_new.A p_new -> alpha.
 // Boundary first: before the sweep all threads compute p_new on the rank's first/last plane and
 // store it straight into the neighbours' ghost planes (P2P) and raise their flags; the sweep runs
@@ -425,7 +472,8 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
       const bool va = ja < jend, vb = ja + 1 < jend;
       const int nsteps = it.k1 - it.k0 + 2;
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;
-      int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);
+      int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);   // plane emitted at step 2
+      int64_t gq = lay_index(L, i, ja, it.dir > 0 ? it.k0 - 1 : it.k1);    // plane loaded at step 0
       PS2 pa, pb, ca, cb, na, nb;
       for (int s = 0; s < nsteps; ++s, ++n) {
         const unsigned st = n % kStages, ph = (n / kStages) & 1u;
@@ -433,29 +481,22 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
         const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
         const bool inb = q >= 0 && q < L.nz;
         mbar_wait(full0 + 8 * st, ph);
-        unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
-        unsigned char* pslab = rs + G.p_bytes;
-        if (active) {
-          for (int row = ly; row < G.RB + 2; row += G.LY) {  // p_new on my share of the slab rows
-            const int off = bx * boxb + (row * BW + col) * 8;
-            const double2 vr = *reinterpret_cast<const double2*>(rs + off);
-            const double2 vp = *reinterpret_cast<const double2*>(pslab + off);
-            double2 vn;
-            vn.x = ghost ? vr.x : vr.x + beta * vp.x;
-            vn.y = ghost ? vr.y : vr.y + beta * vp.y;
-            *reinterpret_cast<double2*>(pslab + off) = vn;
-            const int j = j0 + row - 1;
-            if (inb && row >= 1 && row <= G.RB && j < L.ny) {
-              const int64_t o = lay_index(L, i, j, q);
-              if (pair) *reinterpret_cast<double2*>(pnew + o) = vn;
-              else pnew[o] = vn.x;
-            }
-          }
-        }
-        asm volatile("bar.sync 1, %0;" ::"n"(kNC) : "memory");  // slab of p_new complete (consumers only)
-        if (active) plane_from_slab<KIND>(pslab, tp, ra, na, nb);
+        const unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
+        double2 pna = make_double2(0, 0), pnb = pna;
+        if (active) plane_from_two<KIND>(rs, rs + G.p_bytes, tp, ra, beta, ghost, na, nb, pna, pnb);
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
+        if (inb) {  // my two rows of p_new on the plane just loaded
+          if (va) {
+            if (pair) *reinterpret_cast<double2*>(pnew + gq) = pna;
+            else pnew[gq] = pna.x;
+          }
+          if (vb) {
+            if (pair) *reinterpret_cast<double2*>(pnew + gq + L.pitch) = pnb;
+            else pnew[gq + L.pitch] = pnb.x;
+          }
+        }
+        gq += ps;
         if (s >= 2) {
           const double2 z2 = make_double2(0, 0);
           if (va) emit<KIND, 1>(P, nullptr, pa, ca, na, idx, pair, 0.0, z2, z2, acc);
