@@ -457,6 +457,11 @@ __global__ void __launch_bounds__(kThreads) k_dot(const double* __restrict__ a, 
   }
 }
 
+// Last node of a conditional-WHILE graph body: keep looping while the solve is still running.
+__global__ void k_cond_guard(const __grid_constant__ RankDev P, cudaGraphConditionalHandle h) {
+  if (threadIdx.x == 0) cudaGraphSetConditional(h, P.ctrl->s.done == 0 ? 1u : 0u);
+}
+
 template <class K>
 int occ_grid(K kernel, int device, int cap) {
   int nsm = 0, occ = 0;
@@ -534,6 +539,11 @@ cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* 
     case 16: k_spmv_csr<16><<<grid, kThreads, 0, s>>>(P, in, out, mode); break;
     default: k_spmv_csr<32><<<grid, kThreads, 0, s>>>(P, in, out, mode); break;
   }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_cond_guard(const RankDev& P, unsigned long long handle, cudaStream_t s) {
+  k_cond_guard<<<1, 32, 0, s>>>(P, (cudaGraphConditionalHandle)handle);
   return cudaGetLastError();
 }
 

@@ -53,6 +53,9 @@ cudaError_t launch_pupdate(const RankDev& P, const LaunchCfg& c, double* p, int 
 cudaError_t launch_pipe_start(const RankDev& P, const LaunchCfg& c, int wbuf, cudaStream_t s);
 cudaError_t launch_pipe_update(const RankDev& P, const LaunchCfg& c, int wbuf, cudaStream_t s);
 
+// Sets a CUDA-graph conditional handle to (done == 0): tail of the WHILE-graph body.
+cudaError_t launch_cond_guard(const RankDev& P, unsigned long long handle, cudaStream_t s);
+
 cudaError_t launch_rhs_gen(const RankDev& P, const LaunchCfg& c, int rhs_kind, unsigned long long seed,
                            cudaStream_t s);
 cudaError_t launch_pad(const cgb_layout_t& L, const double* compact, double* padded, cudaStream_t s);

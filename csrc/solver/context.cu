@@ -122,6 +122,8 @@ namespace cgb {
 void ctx_drop_graphs(cgb_ctx* c) {
   for (auto& kv : c->graphs) cudaGraphExecDestroy(kv.second);
   c->graphs.clear();
+  for (auto g : c->while_graphs) cudaGraphDestroy(g);
+  c->while_graphs.clear();
 }
 
 // Resolve neighbour pointers/layouts from the attached peer arenas.
@@ -472,6 +474,58 @@ static int get_graph(cgb_ctx* c, int len, cudaGraphExec_t* out) {
   return CGB_OK;
 }
 
+// One graph for a whole solve: a conditional WHILE node (CUDA >= 12.4) whose body is one
+// iteration (two for the ping-pong variants, so that captured pointers stay valid) followed by a
+// one-thread kernel that keeps the loop alive while the device-resident `done` flag is 0. The
+// host launches it once and synchronises once: no polling, no kernels after convergence.
+static int get_while_graph(cgb_ctx* c, cudaGraphExec_t* out) {
+  const long long key = (1LL << 60) | ((long long)c->opts.variant << 48) | ((long long)c->opts.spmv_impl << 40) |
+                        ((long long)c->host_cur << 36);
+  auto it = c->graphs.find(key);
+  if (it != c->graphs.end()) {
+    *out = it->second;
+    return CGB_OK;
+  }
+  cudaGraph_t g = nullptr;
+  CGB_CUDA(cudaGraphCreate(&g, 0));
+  cudaGraphConditionalHandle h;
+  CGB_CUDA(cudaGraphConditionalHandleCreate(&h, g, 1, cudaGraphCondAssignDefault));
+  cudaGraphNodeParams np = {cudaGraphNodeTypeConditional};
+  np.conditional.handle = h;
+  np.conditional.type = cudaGraphCondTypeWhile;
+  np.conditional.size = 1;
+  cudaGraphNode_t node;
+  CGB_CUDA(cudaGraphAddNode(&node, g, nullptr, 0, &np));
+  cudaGraph_t body = np.conditional.phGraph_out[0];
+  const int saved_cur = c->host_cur;
+  CGB_CUDA(cudaStreamBeginCaptureToGraph(c->stream, body, nullptr, nullptr, 0, cudaStreamCaptureModeThreadLocal));
+  int rc = CGB_OK;
+  for (int i = 0; i < (uses_parity(c) ? 2 : 1) && rc == CGB_OK; ++i) rc = ctx_enqueue_iteration(c, c->stream);
+  if (rc == CGB_OK && launch_cond_guard(c->P, (unsigned long long)h, c->stream) != cudaSuccess)
+    rc = fail(CGB_ERR_CUDA, "launch of the WHILE guard failed");
+  cudaGraph_t dummy = nullptr;
+  cudaError_t e = cudaStreamEndCapture(c->stream, &dummy);
+  c->host_cur = saved_cur;
+  if (rc != CGB_OK) {
+    cudaGraphDestroy(g);
+    return rc;
+  }
+  if (e != cudaSuccess) {
+    cudaGraphDestroy(g);
+    return fail(CGB_ERR_CUDA, "cudaStreamEndCapture (WHILE body): %s", cudaGetErrorString(e));
+  }
+  cudaGraphExec_t ge = nullptr;
+  e = cudaGraphInstantiate(&ge, g, 0);
+  if (e != cudaSuccess) {
+    cudaGraphDestroy(g);
+    return fail(CGB_ERR_CUDA, "cudaGraphInstantiate (WHILE): %s", cudaGetErrorString(e));
+  }
+  c->while_graphs.push_back(g);
+  c->graphs[key] = ge;
+  *out = ge;
+  return CGB_OK;
+}
+
 }  // namespace cgb
 
 // Everything a solve needs that may allocate or synchronise a device: option checks, the extra
@@ -507,7 +561,14 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   if (c->opts.variant == CGB_VAR_PIPELINED) CGB_TRY(ensure_extra(c));
   CGB_TRY(ctx_finalize_peers(c));
   c->stream = pick_stream(c, o->stream);
-  if (c->opts.use_graph) {
+  if (c->opts.use_graph == 2) {
+    cudaGraphExec_t ge;
+    const int saved = c->host_cur;
+    c->host_cur = c->opts.variant == CGB_VAR_PIPELINED ? 1 : 0;  // parity right after begin
+    int rc = get_while_graph(c, &ge);
+    c->host_cur = saved;
+    CGB_TRY(rc);
+  } else if (c->opts.use_graph) {
     cudaGraphExec_t ge;
     const int saved = c->host_cur;
     for (int par = 0; par < (uses_parity(c) ? 2 : 1); ++par) {
@@ -638,6 +699,18 @@ extern "C" int cgb_solve_finish(cgb_ctx* c, cgb_solve_result_t* res) {
 extern "C" int cgb_solve(cgb_ctx* c, const cgb_solve_opts_t* o, cgb_solve_result_t* res) {
   CGB_REQUIRE(c && o && res, "cgb_solve: NULL argument");
   CGB_TRY(cgb_solve_begin(c, o));
+  if (c->opts.use_graph == 2) {
+    cudaGraphExec_t ge;
+    CGB_TRY(get_while_graph(c, &ge));
+    CGB_CUDA(cudaGraphLaunch(ge, c->stream));
+    int rc = cgb_solve_finish(c, res);
+    // kernels that actually ran: init (+2 for pipelined) + per trip (iterations + guard)
+    const int per_trip = uses_parity(c) ? 2 : 1;
+    const int trips = (res->iters + (c->opts.variant == CGB_VAR_PIPELINED ? 1 : 0) + per_trip - 1) / per_trip;
+    res->launches = (c->launches - c->launches_at_begin) + (long long)trips * (per_trip * launches_per_iter(c) + 1);
+    c->launches += (long long)trips * (per_trip * launches_per_iter(c) + 1);
+    return rc;
+  }
   const int chunk = c->opts.chunk, maxit = c->iters_target;
   int slot = 0;
   bool pending[2] = {false, false};

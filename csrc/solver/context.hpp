@@ -50,6 +50,7 @@ struct cgb_ctx {
   long long launches = 0;
   long long launches_at_begin = 0;
   std::map<long long, cudaGraphExec_t> graphs;  // key: variant/impl/length
+  std::vector<cudaGraph_t> while_graphs;        // templates of the conditional-WHILE graphs (own the handles)
   alignas(64) unsigned char tmap[2][128] = {};  // CUtensorMap of exch[0], exch[1] (spmv_tma.cu)
   alignas(64) unsigned char tmap_x[128] = {};   // band-row maps of x and r (update mode)
   alignas(64) unsigned char tmap_r[128] = {};

@@ -151,7 +151,7 @@ class CGSolver:
         o.tol_mode = N.TOL_REL if tol_mode == "rel" else N.TOL_ABS
         o.variant = _VARIANTS[variant]
         o.spmv_impl = _SPMV[spmv]
-        o.use_graph = int(use_graph)
+        o.use_graph = 2 if use_graph == "while" else int(bool(use_graph))
         o.chunk = chunk
         o.fixed_iters = fixed_iters
         o.stream = self._stream(stream)

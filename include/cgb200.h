@@ -165,7 +165,9 @@ typedef struct cgb_solve_opts_t {
   int32_t maxit;         /* reference: 2000 (CUDACG.cu:244) */
   int32_t variant;       /* cgb_variant */
   int32_t spmv_impl;     /* cgb_spmv_impl */
-  int32_t use_graph;     /* capture iteration chunks in CUDA graphs */
+  int32_t use_graph;     /* 0: plain launches; 1: graphs of `chunk` iterations, host polls the device
+                            flag one chunk behind; 2: ONE graph with a conditional WHILE node keyed on
+                            the device flag (cgb_solve only): no polling, nothing runs after convergence */
   int32_t chunk;         /* iterations per graph launch / per host convergence poll */
   int32_t fixed_iters;   /* >0: run exactly this many iterations, convergence test disabled */
   void* stream;          /* cudaStream_t to run on; NULL = context stream */

@@ -160,3 +160,25 @@ def test_merged_variant_matches_oracle(prob):
     np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
     r2 = s.solve(tol=1e-8, variant="merged", chunk=4, use_graph=False)     # repeat on the same context
     assert r2.iters == res.iters and (s.history(n) == h).all()
+
+
+@pytest.mark.parametrize("variant,prob", [("fused", Problem.poisson2d(150, 110)), ("fused", Problem.stencil27(24, 20, 28)),
+                                          ("recompute", Problem.poisson3d(40, 36, 44)), ("merged", Problem.poisson3d(40, 36, 44)),
+                                          ("pipelined", Problem.poisson3d(40, 36, 44)), ("fused", Problem.ref3x3())],
+                         ids=lambda v: v if isinstance(v, str) else v.name)
+def test_while_graph_equals_chunked_graphs(variant, prob):
+    # One conditional-WHILE graph per solve: same iterations and bitwise the same history as the chunked driver.
+    b = prob.rhs("default") if prob.name == "ref3x3" else prob.rhs("random", seed=23)
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    r1 = s.solve(tol=1e-8, variant=variant, use_graph=True, chunk=6)
+    h1 = s.history(r1.iters)
+    x1 = s.x().clone()
+    r2 = s.solve(tol=1e-8, variant=variant, use_graph="while")
+    assert r2.status == r1.status == 1 and r2.iters == r1.iters
+    assert (s.history(r2.iters) == h1).all() and (s.x() == x1).all()
+    r3 = s.solve(tol=1e-30, maxit=9, variant=variant, use_graph="while")
+    assert r3.status == 2 and r3.iters == 9
+    s.set_rhs(np.zeros(prob.n))                      # done is already set at graph entry: the loop must still end
+    r4 = s.solve(variant=variant, use_graph="while")
+    assert r4.iters == 0

@@ -34,6 +34,7 @@ struct Args {
   unsigned long long seed = 0;
   double tol = 1e-7;
   int print_x = -1;  // -1: default (on for small problems)
+  int graph = 1;     // 0 off, 1 chunked graphs, 2 conditional WHILE graph (single GPU driver)
 };
 
 [[noreturn]] void die(const std::string& msg) {
@@ -76,6 +77,10 @@ Args parse(int argc, char** argv) {
     else if (f == "--maxit") a.maxit = std::atoi(need(i).c_str());
     else if (f == "--chunk") a.chunk = std::atoi(need(i).c_str());
     else if (f == "--variant") a.variant = need(i);
+    else if (f == "--graph") {
+      std::string v = need(i);
+      a.graph = v == "while" ? 2 : (v == "off" ? 0 : 1);
+    }
     else if (f == "--spmv") a.spmv = need(i);
     else if (f == "--rhs") {
       a.rhs = need(i);
@@ -93,7 +98,7 @@ Args parse(int argc, char** argv) {
       std::printf("usage: cgb200 [--problem ref3x3|poisson2d5|poisson3d7|stencil3d27|csr:<file.mtx>] [--n NX[,NY[,NZ]]]\n"
                   "              [--gpus P] [--decomp 1d|2d[:PYxPZ]] [--variant auto|fused|recompute|merged|pipelined|cpu] [--spmv auto|simple|tma]\n"
                   "              [--tol T] [--tol-mode abs|rel] [--maxit N] [--rhs ones|random[:seed]|manufactured]\n"
-                  "              [--print-x|--no-print-x] [--x-out F] [--hist-out F] [--json-out F] [--chunk N]\n");
+                  "              [--print-x|--no-print-x] [--x-out F] [--hist-out F] [--json-out F] [--chunk N] [--graph chunk|while|off]\n");
       std::exit(0);
     } else die("unknown option " + f);
   }
@@ -243,6 +248,7 @@ int main(int argc, char** argv) {
                 : a.variant == "fused" ? CGB_VAR_FUSED
                 : a.variant == "recompute" ? CGB_VAR_MERGED
                 : a.variant == "merged" ? CGB_VAR_MERGED2 : CGB_VAR_AUTO;
+      o.use_graph = (P > 1 && a.graph == 2) ? 1 : a.graph;
       o.spmv_impl = a.spmv == "simple" ? CGB_SPMV_SIMPLE : a.spmv == "tma" ? CGB_SPMV_TMA : CGB_SPMV_AUTO;
       if (P == 1) {
         check(cgb_solve(ctx[0], &o, &res), "solve");
