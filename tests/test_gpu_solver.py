@@ -177,8 +177,9 @@ def test_while_graph_equals_chunked_graphs(variant, prob):
     r2 = s.solve(tol=1e-8, variant=variant, use_graph="while")
     assert r2.status == r1.status == 1 and r2.iters == r1.iters
     assert (s.history(r2.iters) == h1).all() and (s.x() == x1).all()
-    r3 = s.solve(tol=1e-30, maxit=9, variant=variant, use_graph="while")
-    assert r3.status == 2 and r3.iters == 9
+    if prob.n > 3:                                   # (the 3x3 system is solved exactly before 9 iterations)
+        r3 = s.solve(tol=1e-30, maxit=9, variant=variant, use_graph="while")
+        assert r3.status == 2 and r3.iters == 9
     s.set_rhs(np.zeros(prob.n))                      # done is already set at graph entry: the loop must still end
     r4 = s.solve(variant=variant, use_graph="while")
     assert r4.iters == 0
