@@ -50,6 +50,7 @@ struct BandGeo {
   int xr_bytes;      // x (or r) slab of the update mode: NBX boxes of RB rows
   int stage_bytes;   // p_bytes (+ 2*xr_bytes in update mode)
   int nstages;
+  int nhalo;         // merged kernel: extra CTAs (on otherwise idle SMs) that only push the boundary planes
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -402,7 +403,13 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     const unsigned pw = (unsigned)((L.nx + 1) / 2);
     const unsigned per_plane = (unsigned)L.ny * pw;
     const unsigned total = ((nb_zlo ? 1u : 0u) + (nb_zhi ? 1u : 0u)) * per_plane;
-    for (unsigned u = blockIdx.x * kNT + threadIdx.x; u < total; u += gridDim.x * kNT) {
+    // With spare SMs, dedicated CTAs (blockIdx >= nitems) push the halo while the band CTAs are
+    // already sweeping; otherwise every CTA takes a share before it starts.
+    const bool dedicated = G.nhalo > 0;
+    const unsigned first = dedicated ? (blockIdx.x >= (unsigned)G.nitems ? (blockIdx.x - G.nitems) * kNT + threadIdx.x : total)
+                                     : blockIdx.x * kNT + threadIdx.x;
+    const unsigned step = (dedicated ? (unsigned)G.nhalo : gridDim.x) * kNT;
+    for (unsigned u = first; u < total; u += step) {
       const unsigned pl = u / per_plane, v = u - pl * per_plane;
       const int j = (int)(v / pw), i = 2 * (int)(v - (unsigned)j * pw);
       const bool lo = pl == 0 && nb_zlo;
@@ -562,6 +569,11 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
   G.nitems = G.nbands * G.zs;
   int g = G.nitems < capacity ? G.nitems : capacity;
   if (g > kMaxGrid) return false;
+  G.nhalo = 0;
+  if (mode == kSpmvPUpdate && P.nbr_mask && g == G.nitems && g < capacity) {
+    G.nhalo = capacity - g < 24 ? capacity - g : 24;
+    g += G.nhalo;
+  }
   *out = G;
   *grid = g;
   *smem = sm;
