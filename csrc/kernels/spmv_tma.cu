@@ -51,6 +51,7 @@ struct BandGeo {
   int stage_bytes;   // p_bytes (+ 2*xr_bytes in update mode)
   int nstages;
   int nhalo;         // merged kernel: extra CTAs (on otherwise idle SMs) that only push the boundary planes
+  int nctas;         // CTAs that sweep bands (= grid - nhalo); items are dealt round-robin over these
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -262,7 +263,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
         asm volatile("fence.proxy.async;" ::: "memory");
         waited = true;
       };
-      for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
+      for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
         if (it.y_ghost) wait_flags();
         const int y0 = it.band * G.RB;  // padded row of band row -1
@@ -304,7 +305,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       xr_off = b * (G.RB * BW * 8) + (ra * BW + col) * 8;
     }
     unsigned n = 0;
-    for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
+    for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
       const int ja = it.band * G.RB + ra;
       const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
@@ -406,22 +407,41 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     // With spare SMs, dedicated CTAs (blockIdx >= nitems) push the halo while the band CTAs are
     // already sweeping; otherwise every CTA takes a share before it starts.
     const bool dedicated = G.nhalo > 0;
-    const unsigned first = dedicated ? (blockIdx.x >= (unsigned)G.nitems ? (blockIdx.x - G.nitems) * kNT + threadIdx.x : total)
+    const unsigned first = dedicated ? (blockIdx.x >= (unsigned)G.nctas ? (blockIdx.x - G.nctas) * kNT + threadIdx.x : total)
                                      : blockIdx.x * kNT + threadIdx.x;
     const unsigned step = (dedicated ? (unsigned)G.nhalo : gridDim.x) * kNT;
-    for (unsigned u = first; u < total; u += step) {
-      const unsigned pl = u / per_plane, v = u - pl * per_plane;
-      const int j = (int)(v / pw), i = 2 * (int)(v - (unsigned)j * pw);
-      const bool lo = pl == 0 && nb_zlo;
-      const int k = lo ? 0 : L.nz - 1;
-      const int d = lo ? dir_index(0, -1) : dir_index(0, 1);
-      const int64_t idx = lay_index(L, i, j, k);
-      const double2 vr = *reinterpret_cast<const double2*>(P.r + idx);
-      double2 vp = *reinterpret_cast<const double2*>(pold + idx);
-      vp.x = vr.x + beta * vp.x;
-      vp.y = vr.y + beta * vp.y;
-      *reinterpret_cast<double2*>(P.nbr_exch[newbuf][d] + ghost_index(P, d, i, j, k)) = vp;
-      atomicAdd(&cnt[d], 1u);
+    for (unsigned u0 = first; u0 < total; u0 += 4 * step) {  // 4 units in flight per thread
+      int64_t src[4], dst[4];
+      int dd[4];
+      double2 vr[4], vp[4];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const unsigned u = u0 + t * step;
+        src[t] = -1;
+        if (u < total) {
+          const unsigned pl = u / per_plane, v = u - pl * per_plane;
+          const int j = (int)(v / pw), i = 2 * (int)(v - (unsigned)j * pw);
+          const bool lo = pl == 0 && nb_zlo;
+          const int k = lo ? 0 : L.nz - 1;
+          dd[t] = lo ? dir_index(0, -1) : dir_index(0, 1);
+          src[t] = lay_index(L, i, j, k);
+          dst[t] = ghost_index(P, dd[t], i, j, k);
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 4; ++t)
+        if (src[t] >= 0) {
+          vr[t] = *reinterpret_cast<const double2*>(P.r + src[t]);
+          vp[t] = *reinterpret_cast<const double2*>(pold + src[t]);
+        }
+#pragma unroll
+      for (int t = 0; t < 4; ++t)
+        if (src[t] >= 0) {
+          vp[t].x = vr[t].x + beta * vp[t].x;
+          vp[t].y = vr[t].y + beta * vp[t].y;
+          *reinterpret_cast<double2*>(P.nbr_exch[newbuf][dd[t]] + dst[t]) = vp[t];
+          atomicAdd(&cnt[dd[t]], 1u);
+        }
     }
     halo_commit(P, cnt, version);
   }
@@ -434,7 +454,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     if (lane == 0) {
       unsigned n = 0;
       bool waited = false;
-      for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
+      for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
         const int y0 = it.band * G.RB;
         const int nsteps = it.k1 - it.k0 + 2;
@@ -471,7 +491,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     tp.r = i + 2 >= L.nx ? -1 : (col + 2 == BW ? (bx + 1) * boxb : tp.c + 16);
     const bool pair = i + 1 < L.nx;
     unsigned n = 0;
-    for (int item = blockIdx.x; item < G.nitems; item += gridDim.x) {
+    for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
       const int j0 = it.band * G.RB;
       const int ja = j0 + ra;
@@ -566,11 +586,23 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
   if (zs < 1) zs = 1;
   G.zchunk = (L.nz + zs - 1) / zs;
   G.zs = (L.nz + G.zchunk - 1) / G.zchunk;
+  const bool nb_lo = P.nbr[dir_index(0, -1)] >= 0, nb_hi = P.nbr[dir_index(0, 1)] >= 0;
+  bool halves = false;
+  if (mode == kSpmvPUpdate && nb_lo && nb_hi && G.zs == 1 && L.nz >= 4) {
+    halves = true;
+    // A rank with neighbours on both sides would need one ghost plane at the very start of a
+    // single upward sweep, i.e. before the neighbour has pushed it. Two half sweeps, each towards
+    // its own ghost plane, need both ghost planes last (a CTA runs them back to back).
+    G.zchunk = (L.nz + 1) / 2;
+    G.zs = 2;
+  }
   G.nitems = G.nbands * G.zs;
   int g = G.nitems < capacity ? G.nitems : capacity;
+  if (halves && G.nbands <= capacity) g = G.nbands;  // same band, both halves, on one CTA
   if (g > kMaxGrid) return false;
+  G.nctas = g;
   G.nhalo = 0;
-  if (mode == kSpmvPUpdate && P.nbr_mask && g == G.nitems && g < capacity) {
+  if (mode == kSpmvPUpdate && P.nbr_mask && g < capacity) {
     G.nhalo = capacity - g < 24 ? capacity - g : 24;
     g += G.nhalo;
   }
