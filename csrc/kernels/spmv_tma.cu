@@ -263,7 +263,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
         asm volatile("fence.proxy.async;" ::: "memory");
         waited = true;
       };
-      for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
+      for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
         if (it.y_ghost) wait_flags();
         const int y0 = it.band * G.RB;  // padded row of band row -1
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       xr_off = b * (G.RB * BW * 8) + (ra * BW + col) * 8;
     }
     unsigned n = 0;
-    for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
+    for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
       const int ja = it.band * G.RB + ra;
       const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     if (lane == 0) {
       unsigned n = 0;
       bool waited = false;
-      for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
+      for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
         const int y0 = it.band * G.RB;
         const int nsteps = it.k1 - it.k0 + 2;
@@ -491,7 +491,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     tp.r = i + 2 >= L.nx ? -1 : (col + 2 == BW ? (bx + 1) * boxb : tp.c + 16);
     const bool pair = i + 1 < L.nx;
     unsigned n = 0;
-    for (int item = blockIdx.x; item < G.nitems; item += G.nctas) {
+    for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
       const int j0 = it.band * G.RB;
       const int ja = j0 + ra;
