@@ -113,7 +113,7 @@ extern "C" int cgb_op_spmv_csr(int32_t n, const int32_t* rowptr, const int32_t* 
   int nnz_last = 0;
   CGB_CUDA(cudaMemcpyAsync(&nnz_last, rowptr + n, sizeof(int), cudaMemcpyDeviceToHost, s));
   CGB_CUDA(cudaStreamSynchronize(s));
-  P.ntx = (nnz_last + n - 1) / n;
+  P.csr_avg_nnz = (nnz_last + n - 1) / n;
   CGB_CUDA(launch_spmv_csr(P, *cfg, x, y, dot_out ? kSpmvDot : kSpmvPlain, s));
   if (dot_out) CGB_CUDA(cudaMemcpyAsync(dot_out, &P.ctrl->s.last_sum[0], sizeof(double), cudaMemcpyDeviceToDevice, s));
   return CGB_OK;

@@ -60,8 +60,10 @@ __device__ __forceinline__ void push_pair(const RankDev& P, int exch_buf, unsign
 // k_init: r = b, p = b, x = 0 (the reference never initialises x on the device, CUDACG.cu:182-186),
 // rho = b.b (CUDACG.cu:261-266 without the sqrt/square round trip), halo push of p0.
 // ---------------------------------------------------------------------------------------------
+// x0_mode = 1 (warm start / restart from a checkpointed x): r = b - A x0 where A x0 was left in P.Ap by
+// a plain SpMV, and x is kept.
 __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankDev P, double tol, int tol_mode,
-                                                    int maxit, int bump_halo) {
+                                                    int maxit, int bump_halo, int x0_mode) {
   __shared__ double red_smem[64];
   __shared__ unsigned cnt[CGB_NDIR];
   Scalars& S = P.ctrl->s;
@@ -86,9 +88,15 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
       if (!mask) continue;
       int64_t idx = lay_index(L, i, j, k);
       double2 v = ld2(P.b + idx);
+      if (x0_mode) {
+        const double2 ax = ld2(P.Ap + idx);
+        v.x -= ax.x;
+        v.y -= ax.y;
+      } else {
+        st2(P.x + idx, zero2);
+      }
       st2(P.r + idx, v);
       st2(p + idx, v);
-      st2(P.x + idx, zero2);
       acc += v.x * v.x + v.y * v.y;
       push_pair(P, 0, mask, i, j, k, v, cnt);
     }
@@ -101,9 +109,15 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
     if (P.nbr_mask && (row_push_mask(L, j, k) & P.nbr_mask)) continue;
     int64_t idx = lay_index(L, i, j, k);
     double2 v = ld2(P.b + idx);
+    if (x0_mode) {
+      const double2 ax = ld2(P.Ap + idx);
+      v.x -= ax.x;
+      v.y -= ax.y;
+    } else {
+      st2(P.x + idx, zero2);
+    }
     st2(P.r + idx, v);
     st2(p + idx, v);
-    st2(P.x + idx, zero2);
     acc += v.x * v.x + v.y * v.y;
   }
   double a = acc, z = 0.0;
@@ -125,6 +139,55 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
       S.beta = 0.0;
       S.halo_seq = version + (bump_halo ? 1 : 0);
       S.done = !ok ? (int)CGB_ERR_TIMEOUT : (isfinite(a) && a > 0.0 ? 0 : (a == 0.0 ? 1 : (int)CGB_ERR_BREAKDOWN));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_stage_x0: exchange buffer 0 := x (owned cells) with the boundary rows pushed to the neighbours,
+// so that a plain SpMV can form A x0 for a warm start.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_stage_x0(const __grid_constant__ RankDev P) {
+  __shared__ double red_smem[64];
+  __shared__ unsigned cnt[CGB_NDIR];
+  Scalars& S = P.ctrl->s;
+  const cgb_layout_t& L = P.lay;
+  const u64 version = S.halo_seq + 1;
+  if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  double* __restrict__ p = P.exch[0];
+  const UnitMap um{(L.nx + 1) / 2, L.ny};
+  const unsigned stride = gridDim.x * kThreads;
+  const unsigned tid0 = blockIdx.x * kThreads + threadIdx.x;
+  if (P.nbr_mask) {
+    const BRows B = brows_make(L);
+    const unsigned UA = (unsigned)B.total * (unsigned)um.pw;
+    for (unsigned u = tid0; u < UA; u += stride) {
+      unsigned brow = u / (unsigned)um.pw;
+      int i = 2 * (int)(u - brow * (unsigned)um.pw), j, k;
+      brow_to_jk(B, L, (int)brow, j, k);
+      unsigned mask = row_push_mask(L, j, k) & P.nbr_mask;
+      if (!mask) continue;
+      int64_t idx = lay_index(L, i, j, k);
+      double2 v = ld2(P.x + idx);
+      st2(p + idx, v);
+      push_pair(P, 0, mask, i, j, k, v, cnt);
+    }
+    halo_commit(P, cnt, version);
+  }
+  const unsigned U = (unsigned)(L.ny * L.nz) * (unsigned)um.pw;
+  for (unsigned u = tid0; u < U; u += stride) {
+    int i, j, k;
+    unit_to_ijk(um, u, i, j, k);
+    if (P.nbr_mask && (row_push_mask(L, j, k) & P.nbr_mask)) continue;
+    int64_t idx = lay_index(L, i, j, k);
+    st2(p + idx, ld2(P.x + idx));
+  }
+  double a = 0.0, z = 0.0;
+  if (grid_sum2_last(a, z, P.partials, &S.ticket_red, red_smem)) {  // only to elect the last CTA
+    if (threadIdx.x == 0) {
+      S.halo_seq = version;
+      S.done = 0;  // a previous solve may have left its final status here; the SpMV must run
     }
   }
 }
@@ -501,9 +564,14 @@ void choose_spmv_tiling(RankDev& P, int grid_spmv) {
   }
 }
 
+cudaError_t launch_stage_x0(const RankDev& P, const LaunchCfg& c, cudaStream_t s) {
+  k_stage_x0<<<c.grid_ew, kThreads, 0, s>>>(P);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit, int bump_halo,
-                        cudaStream_t s) {
-  k_init<<<c.grid_ew, kThreads, 0, s>>>(P, tol, tol_mode, maxit, bump_halo);
+                        int x0_mode, cudaStream_t s) {
+  k_init<<<c.grid_ew, kThreads, 0, s>>>(P, tol, tol_mode, maxit, bump_halo, x0_mode);
   return cudaGetLastError();
 }
 
@@ -525,7 +593,7 @@ cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* 
                             cudaStream_t s) {
   const int n = P.lay.nx;
   // lanes per row ~ average nonzeros per row, rounded to a power of two
-  long long nnz_avg = P.ntx;  // host stores ceil(nnz/n) here for CSR problems
+  const long long nnz_avg = P.csr_avg_nnz;
   int G = 2;
   while (G < 32 && G < nnz_avg) G <<= 1;
   int gpb = kThreads / G;

@@ -28,8 +28,11 @@ void choose_spmv_tiling(RankDev& P, int grid_spmv);
 // r = b, p = b, x = 0, push p's boundary rows, rho = all-reduce(b.b), thresh, iter = 0.
 // bump_halo: the next kernel that pushes halos is not preceded by an x/r update (merged variant), so
 // the version it will publish is announced here.
+// x0_mode: r = b - (A x0 found in P.Ap), x kept (warm start).
 cudaError_t launch_init(const RankDev& P, const LaunchCfg& c, double tol, int tol_mode, int maxit, int bump_halo,
-                        cudaStream_t s);
+                        int x0_mode, cudaStream_t s);
+// exchange buffer 0 := x with halo push (first step of a warm start).
+cudaError_t launch_stage_x0(const RankDev& P, const LaunchCfg& c, cudaStream_t s);
 // out = A in (+ reduction according to mode); simple = register-marching kernel.
 cudaError_t launch_spmv_simple(const RankDev& P, const LaunchCfg& c, const double* in, double* out,
                                int mode, cudaStream_t s);

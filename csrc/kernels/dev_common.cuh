@@ -86,6 +86,7 @@ struct RankDev {
   const int* csr_rowptr;
   const int* csr_colind;
   const double* csr_val;
+  int csr_avg_nnz;   // ceil(nnz/n): picks the lanes-per-row of k_spmv_csr
   // SpMV work decomposition (host-chosen)
   int ntx, nty, nmc, mchunk;
 };

@@ -214,7 +214,7 @@ extern "C" int cgb_ctx_create_csr(int32_t n, int64_t nnz, const int32_t* rowptr,
   c->P.csr_rowptr = c->d_rowptr;
   c->P.csr_colind = c->d_colind;
   c->P.csr_val = c->d_val;
-  c->P.ntx = (int)((nnz + n - 1) / n);  // average row length, picks lanes-per-row
+  c->P.csr_avg_nnz = (int)((nnz + n - 1) / n);
   *out = c;
   return CGB_OK;
 }
@@ -335,6 +335,22 @@ extern "C" int cgb_ctx_set_rhs(cgb_ctx* c, const double* src, int src_is_device,
     dsrc = c->compact_tmp;
   }
   CGB_CUDA(launch_pad(c->lay, dsrc, c->P.b, s));
+  c->launches += 1;
+  if (!stream) CGB_CUDA(cudaStreamSynchronize(c->own_stream));
+  return CGB_OK;
+}
+
+extern "C" int cgb_ctx_set_x0(cgb_ctx* c, const double* src, int src_is_device, void* stream) {
+  CGB_REQUIRE(c && src, "cgb_ctx_set_x0: NULL argument");
+  CGB_CUDA(cudaSetDevice(c->device));
+  cudaStream_t s = pick_stream(c, stream);
+  const double* dsrc = src;
+  if (!src_is_device) {
+    CGB_TRY(ensure_compact_tmp(c));
+    CGB_CUDA(cudaMemcpyAsync(c->compact_tmp, src, (size_t)c->lay.owned * sizeof(double), cudaMemcpyHostToDevice, s));
+    dsrc = c->compact_tmp;
+  }
+  CGB_CUDA(launch_pad(c->lay, dsrc, c->P.x, s));
   c->launches += 1;
   if (!stream) CGB_CUDA(cudaStreamSynchronize(c->own_stream));
   return CGB_OK;
@@ -585,8 +601,17 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
   NvtxRange nvtx_("cgb.solve_begin");
   CGB_TRY(cgb_solve_prepare(c, o));
   c->launches_at_begin = c->launches;
+  if (c->opts.warm_start) {
+    // r0 = b - A x0: stage x0 as SpMV input (with halos), multiply, then the usual init on the residual
+    CGB_CUDA(launch_stage_x0(c->P, c->cfg, c->stream));
+    const RankDev& P = c->P;
+    if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.Ap, kSpmvPlain, c->stream));
+    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], nullptr, nullptr, P.Ap, kSpmvPlain, c->stream));
+    else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.Ap, kSpmvPlain, c->stream));
+    c->launches += 2;
+  }
   CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit,
-                       c->opts.variant == CGB_VAR_MERGED2 ? 1 : 0, c->stream));
+                       c->opts.variant == CGB_VAR_MERGED2 ? 1 : 0, c->opts.warm_start ? 1 : 0, c->stream));
   c->launches += 1;
   c->host_cur = 0;
   c->iters_target = c->opts.maxit;

@@ -54,7 +54,7 @@ class CpuResult(C.Structure):
 class SolveOpts(C.Structure):
     _fields_ = [("tol", C.c_double), ("tol_mode", C.c_int32), ("maxit", C.c_int32), ("variant", C.c_int32),
                 ("spmv_impl", C.c_int32), ("use_graph", C.c_int32), ("chunk", C.c_int32),
-                ("fixed_iters", C.c_int32), ("stream", C.c_void_p)]
+                ("fixed_iters", C.c_int32), ("warm_start", C.c_int32), ("stream", C.c_void_p)]
 
 
 class SolveResult(C.Structure):
@@ -100,6 +100,7 @@ def _declare(lib):
         "cgb_ctx_fabric_reset": (C.c_int, [vp]),
         "cgb_ctx_set_rhs_generated": (C.c_int, [vp, C.c_int, C.c_uint64, vp]),
         "cgb_ctx_set_rhs": (C.c_int, [vp, vp, C.c_int, vp]),
+        "cgb_ctx_set_x0": (C.c_int, [vp, vp, C.c_int, vp]),
         "cgb_ctx_get_x": (C.c_int, [vp, vp, C.c_int, vp]),
         "cgb_ctx_get_history": (C.c_int, [vp, vp, C.c_int]),
         "cgb_solve": (C.c_int, [vp, P(SolveOpts), P(SolveResult)]),

@@ -129,6 +129,36 @@ class CGSolver:
         N.check(L.cgb_ctx_set_rhs(self._ctx, C.c_void_p(b.data_ptr()), 1 if b.is_cuda else 0, s))
         self._keep = b  # keep the source alive until the stream has consumed it
 
+    def set_x0(self, x0, stream=None) -> None:
+        """Initial guess for ``solve(warm_start=True)``: this rank's owned box (numpy or torch, host or device)."""
+        L = N.lib()
+        s = self._stream(stream)
+        if isinstance(x0, np.ndarray):
+            x0 = np.ascontiguousarray(x0, dtype=np.float64)
+            assert x0.size == self.n_local
+            N.check(L.cgb_ctx_set_x0(self._ctx, x0.ctypes.data, 0, s))
+            import torch
+            torch.cuda.current_stream(self.device).synchronize()
+            return
+        import torch
+        assert x0.dtype == torch.float64 and x0.is_contiguous() and x0.numel() == self.n_local
+        N.check(L.cgb_ctx_set_x0(self._ctx, C.c_void_p(x0.data_ptr()), 1 if x0.is_cuda else 0, s))
+        self._keep_x0 = x0
+
+    # Checkpoint = the iterate (plus bookkeeping). Resuming restarts CG from it (r0 = b - A x): the
+    # Krylov space is rebuilt, which is the standard restart of an unpreconditioned CG. The reference
+    # has no checkpointing at all (nothing is ever written to disk, SURVEY.md 5.4).
+    def save_checkpoint(self, path, iters_done: int = 0) -> None:
+        np.savez(path, x=self.x().cpu().numpy(), rank=self.rank, nranks=self.nranks, iters_done=iters_done,
+                 dims=np.array(self.problem.dims), box=np.array([self.part.y0, self.part.ny, self.part.z0, self.part.nz]))
+
+    def load_checkpoint(self, path) -> int:
+        ck = np.load(path)
+        if int(ck["rank"]) != self.rank or int(ck["nranks"]) != self.nranks or tuple(ck["dims"]) != tuple(self.problem.dims):
+            raise ValueError("checkpoint does not belong to this rank/partition/problem")
+        self.set_x0(ck["x"])
+        return int(ck["iters_done"])
+
     def x(self, out=None, stream=None):
         """Owned part of the solution as a device tensor (compact, x fastest)."""
         import torch
@@ -144,7 +174,7 @@ class CGSolver:
         return h
 
     # ---- solve --------------------------------------------------------------------------
-    def _fill_opts(self, tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream):
+    def _fill_opts(self, tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start=False):
         o = self._opts
         o.tol = tol
         o.maxit = maxit
@@ -154,28 +184,32 @@ class CGSolver:
         o.use_graph = 2 if use_graph == "while" else int(bool(use_graph))
         o.chunk = chunk
         o.fixed_iters = fixed_iters
+        o.warm_start = int(bool(warm_start))
         o.stream = self._stream(stream)
         return o
 
     def solve(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "auto",
               spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0,
-              stream=None) -> SolveResult:
-        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
+              stream=None, warm_start: bool = False) -> SolveResult:
+        """warm_start: start from the x the solver holds (``set_x0`` / ``load_checkpoint`` / the previous solve)
+        instead of the reference's x0 = 0: r0 = b - A x0."""
+        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start)
         r = N.SolveResult()
         N.check(N.lib().cgb_solve(self._ctx, C.byref(o), C.byref(r)))
         return SolveResult(r.iters, r.status, r.r0norm, r.rnorm, r.device_ms, r.launches)
 
     # Split-phase API (bench.py times `iterate` between CUDA events on the caller's stream).
     def begin(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "auto",
-              spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0, stream=None):
-        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream)
+              spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0, stream=None,
+              warm_start: bool = False):
+        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start)
         N.check(N.lib().cgb_solve_begin(self._ctx, C.byref(o)))
 
     def prepare(self, **kw):
         """Allocate and capture everything `begin(**kw)` would, without launching. Needed only when one
         host thread drives several ranks (see cgb_solve_prepare)."""
         args = dict(tol=1e-7, maxit=2000, tol_mode="abs", variant="auto", spmv="auto", use_graph=True, chunk=25,
-                    fixed_iters=0, stream=None)
+                    fixed_iters=0, stream=None, warm_start=False)
         args.update(kw)
         o = self._fill_opts(**args)
         N.check(N.lib().cgb_solve_prepare(self._ctx, C.byref(o)))

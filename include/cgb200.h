@@ -170,6 +170,9 @@ typedef struct cgb_solve_opts_t {
                             the device flag (cgb_solve only): no polling, nothing runs after convergence */
   int32_t chunk;         /* iterations per graph launch / per host convergence poll */
   int32_t fixed_iters;   /* >0: run exactly this many iterations, convergence test disabled */
+  int32_t warm_start;    /* 0: x0 = 0 like the reference (CUDACG.cu:177-179, 247); 1: start from the x the
+                            context holds (cgb_ctx_set_x0 or the previous solve): r0 = b - A x0. This is
+                            also the restart path of a checkpoint (x + iteration count). */
   void* stream;          /* cudaStream_t to run on; NULL = context stream */
 } cgb_solve_opts_t;
 void cgb_solve_opts_default(cgb_solve_opts_t* o);
@@ -207,6 +210,8 @@ int cgb_ctx_set_rhs_generated(cgb_ctx* c, int rhs_kind, uint64_t seed, void* str
 /* b given as this rank's compact owned box (nx*ny*nz, x fastest); src may be host (pinned for
  * async) or device memory. */
 int cgb_ctx_set_rhs(cgb_ctx* c, const double* src, int src_is_device, void* stream);
+/* Initial guess for a warm start: this rank's compact owned box, host or device memory. */
+int cgb_ctx_set_x0(cgb_ctx* c, const double* src, int src_is_device, void* stream);
 /* Copy the owned part of x into a compact buffer (host or device). */
 int cgb_ctx_get_x(cgb_ctx* c, double* dst, int dst_is_device, void* stream);
 /* Copy residual history [0,n) to host memory. hist[i] = ||r|| after iteration i. */

@@ -94,3 +94,23 @@ def test_gpu_single_process_multi_gpu(cli, tmp_path):
         ref = cpu_cg(prob, prob.rhs("random", seed=4), tol=1e-8)
         hist = np.array([float(l.split()[1]) for l in h.read_text().splitlines()])
         assert abs(len(hist) - ref.iters) <= 2
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_gpu_multi_gpu_restart_from_x_file(cli, tmp_path):
+    # checkpoint = x written by --x-out; --x0 restarts from it (r0 = b - A x0) on 2 GPUs incl. the halo of x0
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    common = ["--problem", "poisson3d7", "--n", "40,36,44", "--gpus", "2", "--rhs", "random:6", "--tol", "1e-9"]
+    xa, xb, xc = tmp_path / "a.txt", tmp_path / "b.txt", tmp_path / "c.txt"
+    ja, jc = tmp_path / "a.json", tmp_path / "c.json"
+    assert run(cli, *common, "--x-out", str(xa), "--json-out", str(ja)).returncode == 0
+    assert run(cli, *common, "--maxit", "40", "--x-out", str(xb)).returncode == 0
+    r = run(cli, *common, "--x0", str(xb), "--x-out", str(xc), "--json-out", str(jc))
+    assert r.returncode == 0, r.stdout
+    a, c = np.loadtxt(xa), np.loadtxt(xc)
+    np.testing.assert_allclose(c, a, atol=1e-7 * np.abs(a).max())
+    full, resumed = json.loads(ja.read_text()), json.loads(jc.read_text())
+    assert resumed["status"] == 1 and resumed["r0norm"] < full["r0norm"]

@@ -183,3 +183,30 @@ def test_while_graph_equals_chunked_graphs(variant, prob):
     s.set_rhs(np.zeros(prob.n))                      # done is already set at graph entry: the loop must still end
     r4 = s.solve(variant=variant, use_graph="while")
     assert r4.iters == 0
+
+
+@pytest.mark.parametrize("variant,prob", [("fused", Problem.poisson2d(96, 80)), ("merged", Problem.poisson3d(40, 36, 44)),
+                                          ("pipelined", Problem.stencil27(20, 24, 22)), ("fused", Problem.ref3x3())],
+                         ids=lambda v: v if isinstance(v, str) else v.name)
+def test_warm_start_and_checkpoint_restart(variant, prob, tmp_path):
+    # The reference always starts from x0 = 0 (CUDACG.cu:177-179,247). Warm start: r0 = b - A x0.
+    b = prob.rhs("default") if prob.name == "ref3x3" else prob.rhs("random", seed=29)
+    A = prob.to_scipy()
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    full = s.solve(tol=1e-9, variant=variant)
+    x_full = s.x().cpu().numpy()
+    # interrupted run: a few iterations, checkpoint, "new process", resume
+    part = s.solve(tol=1e-9, variant=variant, maxit=max(1, full.iters // 2))
+    s.save_checkpoint(tmp_path / "ck.npz", iters_done=part.iters)
+    x_part = s.x().cpu().numpy()
+    t = CGSolver(prob)
+    t.set_rhs(b)
+    assert t.load_checkpoint(tmp_path / "ck.npz") == part.iters
+    res = t.solve(tol=1e-9, variant=variant, warm_start=True)
+    assert res.status == 1
+    assert res.r0norm == pytest.approx(np.linalg.norm(b - A @ x_part), rel=1e-9)      # r0 = b - A x0
+    np.testing.assert_allclose(t.x().cpu().numpy(), x_full, atol=1e-7 * max(1.0, np.abs(x_full).max()))
+    # warm start from the converged solution needs no iterations worth mentioning
+    res2 = t.solve(tol=1e-6, variant=variant, warm_start=True)
+    assert res2.iters <= 1

@@ -28,7 +28,7 @@
 namespace {
 
 struct Args {
-  std::string problem = "ref3x3", csr_file, variant = "auto", spmv = "auto", rhs = "ones", x_out, hist_out, json_out;
+  std::string problem = "ref3x3", csr_file, variant = "auto", spmv = "auto", rhs = "ones", x_out, hist_out, json_out, x0_in;
   int n[3] = {0, 0, 0};
   int gpus = 1, decomp = 1, Py = 0, Pz = 0, maxit = 2000, chunk = 25, tol_mode = CGB_TOL_ABS;
   unsigned long long seed = 0;
@@ -92,13 +92,14 @@ Args parse(int argc, char** argv) {
     } else if (f == "--print-x") a.print_x = 1;
     else if (f == "--no-print-x") a.print_x = 0;
     else if (f == "--x-out") a.x_out = need(i);
+    else if (f == "--x0") a.x0_in = need(i);  // warm start / restart from a file written by --x-out
     else if (f == "--hist-out") a.hist_out = need(i);
     else if (f == "--json-out") a.json_out = need(i);
     else if (f == "--help" || f == "-h") {
       std::printf("usage: cgb200 [--problem ref3x3|poisson2d5|poisson3d7|stencil3d27|csr:<file.mtx>] [--n NX[,NY[,NZ]]]\n"
                   "              [--gpus P] [--decomp 1d|2d[:PYxPZ]] [--variant auto|fused|recompute|merged|pipelined|cpu] [--spmv auto|simple|tma]\n"
                   "              [--tol T] [--tol-mode abs|rel] [--maxit N] [--rhs ones|random[:seed]|manufactured]\n"
-                  "              [--print-x|--no-print-x] [--x-out F] [--hist-out F] [--json-out F] [--chunk N] [--graph chunk|while|off]\n");
+                  "              [--print-x|--no-print-x] [--x-out F] [--hist-out F] [--json-out F] [--x0 F] [--chunk N] [--graph chunk|while|off]\n");
       std::exit(0);
     } else die("unknown option " + f);
   }
@@ -238,6 +239,22 @@ int main(int argc, char** argv) {
           if (q != r) check(cgb_ctx_peer_attach_ptr(ctx[(size_t)r], q, cgb_ctx_arena_base(ctx[(size_t)q])), "peer attach");
       for (int r = 0; r < P; ++r) check(cgb_ctx_fabric_reset(ctx[(size_t)r]), "fabric reset");
       for (int r = 0; r < P; ++r) check(cgb_ctx_set_rhs_generated(ctx[(size_t)r], rk, a.seed, nullptr), "rhs");
+      if (!a.x0_in.empty()) {  // scatter the global initial guess to the ranks
+        std::ifstream in(a.x0_in);
+        if (!in) die("cannot open " + a.x0_in);
+        std::vector<double> g((size_t)n_total);
+        for (long long i = 0; i < n_total; ++i)
+          if (!(in >> g[(size_t)i])) die("initial guess file is too short");
+        for (int r = 0; r < P; ++r) {
+          const cgb_partition_t& p = part[(size_t)r];
+          std::vector<double> loc((size_t)p.nx * p.ny * p.nz);
+          for (int k = 0; k < p.nz; ++k)
+            for (int j = 0; j < p.ny; ++j)
+              std::memcpy(&loc[(size_t)p.nx * ((size_t)j + (size_t)p.ny * (size_t)k)],
+                          &g[(size_t)nx * ((size_t)(j + p.y0) + (size_t)ny * (size_t)(k + p.z0))], sizeof(double) * (size_t)p.nx);
+          check(cgb_ctx_set_x0(ctx[(size_t)r], loc.data(), 0, nullptr), "memcpy from host to device (x0)");
+        }
+      }
       cgb_solve_opts_t o;
       cgb_solve_opts_default(&o);
       o.tol = a.tol;
@@ -249,6 +266,7 @@ int main(int argc, char** argv) {
                 : a.variant == "recompute" ? CGB_VAR_MERGED
                 : a.variant == "merged" ? CGB_VAR_MERGED2 : CGB_VAR_AUTO;
       o.use_graph = (P > 1 && a.graph == 2) ? 1 : a.graph;
+      o.warm_start = a.x0_in.empty() ? 0 : 1;
       o.spmv_impl = a.spmv == "simple" ? CGB_SPMV_SIMPLE : a.spmv == "tma" ? CGB_SPMV_TMA : CGB_SPMV_AUTO;
       if (P == 1) {
         check(cgb_solve(ctx[0], &o, &res), "solve");
