@@ -127,7 +127,7 @@ def main():
         grid = grid * (2 if a.problem == "poisson2d5" else 3)
     prob = Problem.from_name(a.problem, grid)
     K, W = a.steps, max(a.warmup, 3)
-    chunk = a.chunk or max(1, min(25, W, K))
+    chunk = a.chunk or max(1, min(25, K))   # graphs are captured and uploaded in begin(), not in the timed region
     stream = torch.cuda.Stream()
     solver = CGSolver(prob, rank=rank, nranks=world, decomp=a.decomp, maxit_cap=max(W + K + 8, 64))
     if world > 1:

@@ -139,24 +139,16 @@ extern "C" int cgb_op_fused_update(const cgb_layout_t* lay, double alpha, const 
   return CGB_OK;
 }
 
-extern "C" int cgb_op_p_update(const cgb_layout_t* lay, double beta, const double* r, double* p, void* stream) {
+extern "C" int cgb_op_p_update(const cgb_layout_t* lay, double beta, const double* r, double* p, void* scratch,
+                               void* stream) {
   CGB_REQUIRE(lay && r && p, "cgb_op_p_update: NULL argument");
   cudaStream_t s = (cudaStream_t)stream;
   LaunchCfg* cfg;
   CGB_TRY(get_cfg(&cfg));
-  // k_pupdate only reads done/beta/halo_seq from the control block; a small private one suffices
-  static thread_local void* ctl = nullptr;
-  static thread_local int ctl_dev = -1;
-  int dev = 0;
-  CGB_CUDA(cudaGetDevice(&dev));
-  if (!ctl || ctl_dev != dev) {
-    CGB_CUDA(cudaMalloc(&ctl, kCtrlBytes));
-    ctl_dev = dev;
-  }
   Scalars img = blank_scalars();
   img.beta = beta;
   RankDev P;
-  CGB_TRY(make_op_rank(nullptr, lay, ctl, img, s, &P));
+  CGB_TRY(make_op_rank(nullptr, lay, scratch, img, s, &P));
   P.r = const_cast<double*>(r);
   CGB_CUDA(launch_pupdate(P, *cfg, p, 0, s));
   return CGB_OK;

@@ -134,7 +134,6 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
       S.iter = 0;
       S.maxit = maxit;
       S.cur = 0;
-      S.pending_x = 0;
       S.alpha = 0.0;
       S.beta = 0.0;
       S.halo_seq = version + (bump_halo ? 1 : 0);

@@ -21,7 +21,7 @@ constexpr int kMaxGrid = 2048;        // upper bound on CTAs of any persistent k
 constexpr int kThreads = 256;         // CTA size of every kernel in this file family
 constexpr size_t kCtrlBytes = 8192;   // control block footprint at arena offset 0
 constexpr size_t kPartialsOff = kCtrlBytes;
-constexpr size_t kPartialsBytes = (size_t)kMaxGrid * 2 * sizeof(double);
+static_assert(kPartialsOff + (size_t)kMaxGrid * sizeof(double2) <= 65536, "partials overlap the exchanged vectors");
 constexpr size_t kExchOff = 65536;    // first exchanged vector; identical on every rank
 
 typedef unsigned long long u64;
@@ -45,8 +45,7 @@ struct Scalars {
   int iter;          // completed iterations
   int done;          // 0 running, 1 converged, 2 maxit, <0 cgb_status
   int maxit;
-  int cur;           // exchange buffer that holds the current SpMV input
-  int pending_x;     // merged variant: x += alpha*p_old still owed
+  int cur;           // pipelined CG: exchange buffer that holds the current w (diagnostic)
   unsigned int ticket_red;
   unsigned int ticket_halo[CGB_NDIR];
 };

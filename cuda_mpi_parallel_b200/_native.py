@@ -118,7 +118,7 @@ def _declare(lib):
         "cgb_op_spmv_stencil": (C.c_int, [P(Stencil), P(Layout), vp, vp, vp, vp, C.c_int, vp]),
         "cgb_op_spmv_csr": (C.c_int, [i32, vp, vp, vp, vp, vp, vp, vp, vp]),
         "cgb_op_fused_update": (C.c_int, [P(Layout), dbl, vp, vp, vp, vp, vp, vp, vp]),
-        "cgb_op_p_update": (C.c_int, [P(Layout), dbl, vp, vp, vp]),
+        "cgb_op_p_update": (C.c_int, [P(Layout), dbl, vp, vp, vp, vp]),
         "cgb_op_pad": (C.c_int, [P(Layout), vp, vp, vp]),
         "cgb_op_unpad": (C.c_int, [P(Layout), vp, vp, vp]),
         "cgb_version": (C.c_char_p, []),

@@ -115,5 +115,5 @@ def p_update(layout: N.Layout, beta: float, r, p):
     for t in (r, p):
         _chk(t, layout.vec_elems)
     with torch.cuda.device(p.device):
-        N.check(N.lib().cgb_op_p_update(C.byref(layout), float(beta), _vp(r), _vp(p), _stream(p)))
+        N.check(N.lib().cgb_op_p_update(C.byref(layout), float(beta), _vp(r), _vp(p), _vp(scratch(p.device)), _stream(p)))
     return p

@@ -268,7 +268,7 @@ int cgb_op_spmv_csr(int32_t n, const int32_t* rowptr, const int32_t* colind, con
 int cgb_op_fused_update(const cgb_layout_t* lay, double alpha, const double* p, const double* Ap,
                         double* x, double* r, double* rr_out, void* scratch, void* stream);
 /* p = r + beta p   (CUDACG.cu:339-347 in one pass) */
-int cgb_op_p_update(const cgb_layout_t* lay, double beta, const double* r, double* p,
+int cgb_op_p_update(const cgb_layout_t* lay, double beta, const double* r, double* p, void* scratch,
                     void* stream);
 /* compact <-> padded copies of one local box */
 int cgb_op_pad(const cgb_layout_t* lay, const double* compact, double* padded, void* stream);
