@@ -27,6 +27,29 @@ def main():
     b = prob.rhs("random", seed=21)
     part = make_partition(prob, world, rank, decomp)
     b_local = scatter_global(prob, part, b)
+    if mode == "soak":
+        # T5: many iterations on a tiny box => thousands of flag handshakes and all-reduces; every rank must
+        # see bit-identical scalars and nothing may dead-lock (waits are bounded by CGB_TIMEOUT_MS).
+        local_rank = int(os.environ["LOCAL_RANK"])
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from cuda_mpi_parallel_b200 import CGSolver
+        from cuda_mpi_parallel_b200.parallel import attach_torch_distributed
+        sol = CGSolver(prob, rank=rank, nranks=world, decomp=decomp, maxit_cap=4000)
+        attach_torch_distributed(sol)
+        ok = True
+        for v in ("fused", "pipelined", variant):
+            sol.set_rhs(b_local)
+            res = sol.solve(fixed_iters=1500, variant=v, chunk=50)
+            h = sol.history(200).tolist()       # before round-off takes over
+            g = [None] * world
+            dist.all_gather_object(g, (res.iters, res.status, h))
+            ok = ok and all(x == g[0] for x in g) and res.iters == 1500 and res.status in (0, 2)
+        if rank == 0:
+            print("MPRESULT " + json.dumps({"ok": bool(ok), "ranks_identical": bool(ok), "world": world}), flush=True)
+        dist.barrier()
+        dist.destroy_process_group()
+        sys.exit(0 if ok else 1)
     if mode == "cpu":
         dist.init_process_group("gloo")
         from cuda_mpi_parallel_b200.parallel.cpu_dist import cpu_dist_cg

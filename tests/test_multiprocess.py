@@ -85,3 +85,14 @@ def test_gpu_fabric_merged_variant(name, dims):
     nproc = 2 if n < 4 else 4
     res = _run(nproc, ["gpu", name, dims, "1", "merged"], port=29760, timeout=240)
     assert res["ok"] and res["ranks_identical"], res
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_gpu_fabric_soak_thousands_of_handshakes():
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nproc = 2 if n < 4 else 4
+    res = _run(nproc, ["soak", "poisson3d7", "32x16x24", "1", "merged"], port=29780, timeout=300)
+    assert res["ok"], res
