@@ -80,6 +80,8 @@ struct RankDev {
   double *x, *r, *Ap, *b, *s, *z, *pp;
   double* hist;
   int hist_cap;
+  double* hist_host;  // optional mapped pinned host buffer: ||r|| of every iteration is also stored there
+  int hist_host_cap;
   double2* partials;
   // CSR problems
   const int* csr_rowptr;
@@ -324,6 +326,7 @@ __device__ __forceinline__ void cg_after_rr(const RankDev& P, double rr) {
   const double rn = sqrt(rr);
   const int it = S.iter;
   if (it < P.hist_cap) P.hist[it] = rn;
+  if (P.hist_host && it < P.hist_host_cap) P.hist_host[it] = rn;  // zero-copy D2H of this step's result
   S.rnorm = rn;
   S.iter = it + 1;
   if (!isfinite(rr)) {

@@ -170,8 +170,9 @@ __global__ void __launch_bounds__(kThreads) k_pipe_update(const __grid_constant_
       if (it == 0) {
         S.r0norm = rn;
         S.thresh = thresh;
-      } else if (it - 1 < P.hist_cap) {
-        P.hist[it - 1] = rn;  // ||r|| after iteration it-1
+      } else {
+        if (it - 1 < P.hist_cap) P.hist[it - 1] = rn;  // ||r|| after iteration it-1
+        if (P.hist_host && it - 1 < P.hist_host_cap) P.hist_host[it - 1] = rn;
       }
       S.rnorm = rn;
       if (!ok) S.done = CGB_ERR_TIMEOUT;

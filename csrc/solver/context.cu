@@ -380,6 +380,27 @@ extern "C" int cgb_ctx_get_history(cgb_ctx* c, double* dst, int n) {
   return CGB_OK;
 }
 
+extern "C" int cgb_ctx_set_host_history(cgb_ctx* c, double* pinned, int cap) {
+  CGB_REQUIRE(c, "cgb_ctx_set_host_history: NULL context");
+  CGB_CUDA(cudaSetDevice(c->device));
+  double* dev = nullptr;
+  if (pinned) {
+    CGB_REQUIRE(cap > 0, "cgb_ctx_set_host_history: cap must be positive");
+    cudaError_t e = cudaHostGetDevicePointer((void**)&dev, pinned, 0);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      return fail(CGB_ERR_INVALID, "cgb_ctx_set_host_history: buffer is not mapped pinned host memory (%s)",
+                  cudaGetErrorString(e));
+    }
+  }
+  if (dev != c->P.hist_host || cap != c->P.hist_host_cap) {
+    c->P.hist_host = dev;
+    c->P.hist_host_cap = pinned ? cap : 0;
+    cgb::ctx_drop_graphs(c);  // captured kernels hold a copy of P
+  }
+  return CGB_OK;
+}
+
 extern "C" int64_t cgb_ctx_launch_count(cgb_ctx* c) { return c ? c->launches : 0; }
 
 // ---------------------------------------------------------------------------------------------

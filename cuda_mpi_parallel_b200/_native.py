@@ -103,6 +103,7 @@ def _declare(lib):
         "cgb_ctx_set_x0": (C.c_int, [vp, vp, C.c_int, vp]),
         "cgb_ctx_get_x": (C.c_int, [vp, vp, C.c_int, vp]),
         "cgb_ctx_get_history": (C.c_int, [vp, vp, C.c_int]),
+        "cgb_ctx_set_host_history": (C.c_int, [vp, vp, C.c_int]),
         "cgb_solve": (C.c_int, [vp, P(SolveOpts), P(SolveResult)]),
         "cgb_solve_begin": (C.c_int, [vp, P(SolveOpts)]),
         "cgb_solve_prepare": (C.c_int, [vp, P(SolveOpts)]),

@@ -168,6 +168,18 @@ class CGSolver:
                                       self._stream(stream)))
         return out
 
+    def set_host_history(self, pinned=None) -> None:
+        """Stream ||r||_2 of every iteration into a pinned host tensor (device-side zero-copy store, no host
+        stall, no extra stream op): the reference reads this scalar back every iteration (CUDACG.cu:328)
+        but blocks the host to do it. Pass None to switch off. Call before solve()/begin()."""
+        if pinned is None:
+            N.check(N.lib().cgb_ctx_set_host_history(self._ctx, None, 0))
+            self._host_hist = None
+            return
+        assert pinned.is_pinned() and pinned.dtype.is_floating_point and pinned.element_size() == 8
+        N.check(N.lib().cgb_ctx_set_host_history(self._ctx, C.c_void_p(pinned.data_ptr()), pinned.numel()))
+        self._host_hist = pinned
+
     def history(self, n: int) -> np.ndarray:
         h = np.zeros(max(n, 0))
         N.check(N.lib().cgb_ctx_get_history(self._ctx, h.ctypes.data, int(n)))

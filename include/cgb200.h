@@ -228,6 +228,11 @@ int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o);
 int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o);
 /* Enqueue up to n more iterations without synchronising the host. */
 int cgb_solve_iterate(cgb_ctx* c, int n);
+/* Host-visible residual history: `pinned` (cudaHostAlloc'ed / torch pinned memory, cap doubles, or NULL to
+ * switch off) receives ||r||_2 of every iteration through a device-side store the moment the iteration's
+ * reduction completes - the reference's per-iteration read-back (CUDACG.cu:328) with no host stall and no
+ * extra stream operation. Set it before cgb_solve_prepare/begin (captured graphs embed the pointer). */
+int cgb_ctx_set_host_history(cgb_ctx* c, double* pinned, int cap);
 /* n iterations, each followed by a stream-ordered 8-byte device->host copy of ||r||_2 into
  * host_hist[i] (pinned memory): the reference's per-iteration residual read-back (CUDACG.cu:328)
  * without stalling the host. */

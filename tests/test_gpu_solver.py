@@ -210,3 +210,22 @@ def test_warm_start_and_checkpoint_restart(variant, prob, tmp_path):
     # warm start from the converged solution needs no iterations worth mentioning
     res2 = t.solve(tol=1e-6, variant=variant, warm_start=True)
     assert res2.iters <= 1
+
+
+def test_host_history_streams_every_residual_to_pinned_memory():
+    import torch
+    prob = Problem.poisson3d(40, 36, 44)
+    s = CGSolver(prob)
+    s.set_rhs("random", seed=31)
+    hist = torch.zeros(600, dtype=torch.float64).pin_memory()
+    s.set_host_history(hist)
+    for variant in ("merged", "pipelined", "fused"):
+        hist.zero_()
+        res = s.solve(tol=1e-8, variant=variant)
+        assert res.status == 1
+        np.testing.assert_array_equal(hist[:res.iters].numpy(), s.history(res.iters))
+        assert float(hist[res.iters]) == 0.0
+    s.set_host_history(None)
+    hist.zero_()
+    s.solve(tol=1e-8)
+    assert float(hist.abs().max()) == 0.0
