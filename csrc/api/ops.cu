@@ -81,11 +81,12 @@ extern "C" int cgb_op_spmv_stencil(const cgb_stencil_t* st, const cgb_layout_t* 
   const bool tma = impl != CGB_SPMV_SIMPLE && spmv_tma_supported(P);
   if (impl == CGB_SPMV_TMA && !tma) return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV needs a 3D stencil problem");
   if (tma) {
-    alignas(64) unsigned char map[128];
+    alignas(64) unsigned char map[128], map_h[128];
     CGB_TRY(spmv_tma_make_map(*lay, p, map));
+    CGB_TRY(spmv_tma_make_map(*lay, p, map_h, 1, 2));
     int dev = 0;
     CGB_CUDA(cudaGetDevice(&dev));
-    CGB_CUDA(launch_spmv_tma(P, dev, map, nullptr, nullptr, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
+    CGB_CUDA(launch_spmv_tma(P, dev, map, map_h, nullptr, nullptr, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
   } else {
     CGB_CUDA(launch_spmv_simple(P, *cfg, p, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));
   }

@@ -38,13 +38,14 @@ cudaError_t launch_spmv_simple(const RankDev& P, const LaunchCfg& c, const doubl
                                int mode, cudaStream_t s);
 // TMA-fed stencil SpMV (spmv_tma.cu). `map` points at a 128-byte CUtensorMap of the input vector.
 bool spmv_tma_supported(const RankDev& P);
-int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows = 1);
-// map_x / map_r (halo_rows = 0 maps of x and r) are needed for mode kSpmvUpdate only.
-cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_x, const void* map_r,
-                            double* out, int mode, cudaStream_t s);
+int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows = 1, int box_cols = 128);
+// map_h: the input's 2-column halo-box map (rows wider than 512 cells). map_x / map_r (halo_rows = 0 maps of
+// x and r) are needed for mode kSpmvUpdate only.
+cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_h, const void* map_x,
+                            const void* map_r, double* out, int mode, cudaStream_t s);
 // "merged" variant: p-update folded into the SpMV (maps: r with halo rows, p_old, p_new buffers).
-cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* map_r, const void* map_pold,
-                             const void* map_pnew, const double* pold, double* pnew, int newbuf, cudaStream_t s);
+cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const maps[6], const double* pold, double* pnew,
+                             int newbuf, cudaStream_t s);
 cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* in, double* out, int mode,
                             cudaStream_t s);
 // x += alpha p; r -= alpha Ap; rho' = all-reduce(r.r); convergence test; beta.

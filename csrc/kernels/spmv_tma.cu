@@ -20,8 +20,11 @@
 //    peer GPU and is read through the async proxy here). Interior planes are therefore computed
 //    while the halo is still in flight.
 //
-// Replaces cusparseSpMV + cublasDdot of the reference (CUDACG.cu:288-304) for 3D stencils with
-// nx <= 512; other shapes use the L1-path kernel.
+//  * Rows wider than 512 cells are cut into 512-cell x tiles; a tile's two x-halo columns arrive
+//    in two extra 2-column boxes per slab (zero-filled by the TMA unit outside the domain).
+//
+// Replaces cusparseSpMV + cublasDdot of the reference (CUDACG.cu:288-304) for 3D stencils; 2D
+// problems and general CSR use the L1-path kernels.
 #include <cuda.h>
 
 #include <mutex>
@@ -37,12 +40,14 @@ constexpr int BW = 128;                  // cells per TMA box row
 constexpr int kNC = 512;                 // consumer threads
 constexpr int kNT = kNC + 32;            // + one producer warp
 constexpr int kMaxStages = 8;
-constexpr int kMaxNx = 512;
+constexpr int kTileX = 512;             // cells per x tile when the row is wider than one tile
 
 struct BandGeo {
   int LX, LY;        // consumer thread grid: LX pair-columns x LY row-pairs
   int RB;            // rows per band = 2*LY
-  int NBX;           // TMA boxes per slab row = ceil(nx/128)
+  int NBX;           // 128-wide TMA boxes per slab row
+  int ntx, nby;      // x tiles (of 2*LX cells) and row bands; nbands = ntx*nby
+  int h_off;         // x-tiled layouts: byte offset of the two 2-column halo boxes inside a p slab
   int nbands;
   int zs, zchunk;    // z split
   int nitems;
@@ -92,7 +97,33 @@ struct PS2 {  // plane sums of one cell pair
 // Byte offsets (within a slab) of a thread's centre pair / left / right neighbour in slab row 0.
 struct Taps {
   int c, l, r;        // l,r < 0: Dirichlet zero
+  int ls, rs;         // bytes between slab rows for the l / r tap (1024 in a main box, 16 in a halo box)
 };
+
+// Offsets of a consumer thread's taps. il = x offset inside the tile, i = global x.
+__device__ __forceinline__ Taps make_taps(const BandGeo& G, int il, int i, int nx) {
+  constexpr int RS = BW * 8;
+  const int boxb = (G.RB + 2) * RS;
+  const int b = il / BW, col = il % BW;
+  Taps tp;
+  tp.c = b * boxb + col * 8;
+  tp.ls = tp.rs = RS;
+  if (il == 0) {
+    tp.l = G.ntx > 1 ? G.h_off + 8 : -1;  // column x0-1 = element 1 of the left halo box (zero-filled at x = -1)
+    if (G.ntx > 1) tp.ls = 16;
+  } else {
+    tp.l = col == 0 ? (b - 1) * boxb + (BW - 1) * 8 : tp.c - 8;
+  }
+  if (G.ntx > 1 && il + 2 == 2 * G.LX) {
+    tp.r = G.h_off + 128;                 // column x0+tile = element 0 of the right halo box
+    tp.rs = 16;
+  } else if (G.ntx == 1 && i + 2 >= nx) {
+    tp.r = -1;
+  } else {
+    tp.r = col + 2 == BW ? (b + 1) * boxb : tp.c + 16;
+  }
+  return tp;
+}
 
 // Plane sums for the thread's two adjacent rows from one slab. Slab row t holds band row t-1.
 template <int KIND>
@@ -100,8 +131,8 @@ __device__ __forceinline__ void plane_from_slab(const unsigned char* slab, const
   constexpr int RS = BW * 8;  // slab row stride in bytes
   const unsigned char* b0 = slab + ra * RS;
   auto ld2 = [&](int row) { return *reinterpret_cast<const double2*>(b0 + row * RS + tp.c); };
-  auto ldl = [&](int row) { return tp.l >= 0 ? *reinterpret_cast<const double*>(b0 + row * RS + tp.l) : 0.0; };
-  auto ldr = [&](int row) { return tp.r >= 0 ? *reinterpret_cast<const double*>(b0 + row * RS + tp.r) : 0.0; };
+  auto ldl = [&](int row) { return tp.l >= 0 ? *reinterpret_cast<const double*>(slab + tp.l + (ra + row) * tp.ls) : 0.0; };
+  auto ldr = [&](int row) { return tp.r >= 0 ? *reinterpret_cast<const double*>(slab + tp.r + (ra + row) * tp.rs) : 0.0; };
   const double2 c0 = ld2(0), c1 = ld2(1), c2 = ld2(2), c3 = ld2(3);
   const double l1 = ldl(1), q1 = ldr(1), l2 = ldl(2), q2 = ldr(2);
   A.s0[0] = c1.x; A.s0[1] = c1.y;
@@ -138,14 +169,12 @@ __device__ __forceinline__ void plane_from_two(const unsigned char* rslab, const
     return make_double2(vr.x + bt * vp.x, vr.y + bt * vp.y);
   };
   auto pnl = [&](int row) {
-    return tp.l >= 0 ? *reinterpret_cast<const double*>(r0 + row * RS + tp.l) +
-                           bt * *reinterpret_cast<const double*>(p0 + row * RS + tp.l)
-                     : 0.0;
+    const int o = tp.l + (ra + row) * tp.ls;
+    return tp.l >= 0 ? *reinterpret_cast<const double*>(rslab + o) + bt * *reinterpret_cast<const double*>(pslab + o) : 0.0;
   };
   auto pnr = [&](int row) {
-    return tp.r >= 0 ? *reinterpret_cast<const double*>(r0 + row * RS + tp.r) +
-                           bt * *reinterpret_cast<const double*>(p0 + row * RS + tp.r)
-                     : 0.0;
+    const int o = tp.r + (ra + row) * tp.rs;
+    return tp.r >= 0 ? *reinterpret_cast<const double*>(rslab + o) + bt * *reinterpret_cast<const double*>(pslab + o) : 0.0;
   };
   const double2 c0 = pn2(0), c1 = pn2(1), c2 = pn2(2), c3 = pn2(3);
   const double l1 = pnl(1), q1 = pnr(1), l2 = pnl(2), q2 = pnr(2);
@@ -205,6 +234,7 @@ __device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out,
 
 struct Item {
   int band, k0, k1, dir;
+  int x0, yb;        // first cell of the x tile, row-band index
   bool y_ghost;
 };
 __device__ __forceinline__ Item make_item(const RankDev& P, const BandGeo& G, int item, bool nb_zlo, bool nb_zhi,
@@ -216,13 +246,16 @@ __device__ __forceinline__ Item make_item(const RankDev& P, const BandGeo& G, in
   it.k1 = min(P.lay.nz, it.k0 + G.zchunk);
   const bool lo = it.k0 == 0 && nb_zlo, hi = it.k1 == P.lay.nz && nb_zhi;
   it.dir = (lo && !hi) ? -1 : 1;  // sweep towards the only ghost plane so that it is loaded last
-  it.y_ghost = (it.band == 0 && nb_ylo) || (it.band == G.nbands - 1 && nb_yhi);
+  it.x0 = (it.band % G.ntx) * 2 * G.LX;
+  it.yb = it.band / G.ntx;
+  it.y_ghost = (it.yb == 0 && nb_ylo) || (it.yb == G.nby - 1 && nb_yhi);
   return it;
 }
 
 template <int KIND, int OUT>
 __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ RankDev P,
                                                       const __grid_constant__ CUtensorMap tmap,
+                                                      const __grid_constant__ CUtensorMap tmap_h,
                                                       const __grid_constant__ CUtensorMap tmx,
                                                       const __grid_constant__ CUtensorMap tmr,
                                                       const __grid_constant__ BandGeo G, double* __restrict__ out,
@@ -266,23 +299,29 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
         if (it.y_ghost) wait_flags();
-        const int y0 = it.band * G.RB;  // padded row of band row -1
+        const int y0 = it.yb * G.RB;  // padded row of band row -1
         const int nsteps = it.k1 - it.k0 + 2;
+        const unsigned p_tx = (unsigned)(G.NBX * (G.RB + 2) * BW * 8 + (G.ntx > 1 ? 2 * (G.RB + 2) * 16 : 0));
         for (int s = 0; s < nsteps; ++s, ++n) {
           const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
           if ((q == -1 && nb_zlo) || (q == L.nz && nb_zhi)) wait_flags();
           const unsigned st = n % kStages, ph = (n / kStages) & 1u;
           mbar_wait(empty0 + 8 * st, ph ^ 1u);
           const bool with_xr = OUT == 2 && s >= 2;  // this step emits a plane: bring its x and r rows too
-          mbar_expect_tx(full0 + 8 * st, (unsigned)(G.p_bytes + (with_xr ? 2 * G.xr_bytes : 0)));
+          mbar_expect_tx(full0 + 8 * st, p_tx + (with_xr ? 2u * (unsigned)G.xr_bytes : 0u));
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
           for (int b = 0; b < G.NBX; ++b)
-            tma_load_3d(dst + b * (G.RB + 2) * BW * 8, &tmap, b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + b * (G.RB + 2) * BW * 8, &tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+          if (G.ntx > 1) {  // the tile's x halo: two 2-column boxes (zero-filled outside the domain)
+            tma_load_3d(dst + G.h_off, &tmap_h, it.x0 - 2, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.h_off + 128, &tmap_h, it.x0 + 2 * G.LX, y0, q + 1, full0 + 8 * st);
+          }
           if (with_xr) {
             const int ko = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
             for (int b = 0; b < G.NBX; ++b) {
-              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, &tmx, b * BW, y0 + 1, ko + 1, full0 + 8 * st);
-              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, &tmr, b * BW, y0 + 1, ko + 1, full0 + 8 * st);
+              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, &tmx, it.x0 + b * BW, y0 + 1, ko + 1, full0 + 8 * st);
+              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, &tmr, it.x0 + b * BW, y0 + 1, ko + 1,
+                          full0 + 8 * st);
             }
           }
         }
@@ -291,24 +330,17 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
   } else {
     // ===== consumer warps =====
     const int lx = threadIdx.x % G.LX, ly = threadIdx.x / G.LX;
-    const int i = 2 * lx;
-    const bool active = ly < G.LY && i < L.nx;
+    const int il = 2 * lx;
     const int ra = 2 * ly;
-    Taps tp;
-    int xr_off;
-    {
-      const int b = i / BW, col = i % BW;
-      const int boxb = (G.RB + 2) * BW * 8;
-      tp.c = b * boxb + col * 8;
-      tp.l = i == 0 ? -1 : (col == 0 ? (b - 1) * boxb + (BW - 1) * 8 : tp.c - 8);
-      tp.r = i + 2 >= L.nx ? -1 : (col + 2 == BW ? (b + 1) * boxb : tp.c + 16);
-      xr_off = b * (G.RB * BW * 8) + (ra * BW + col) * 8;
-    }
+    const int xr_off = (il / BW) * (G.RB * BW * 8) + (ra * BW + il % BW) * 8;
     unsigned n = 0;
     for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
-      const int ja = it.band * G.RB + ra;
-      const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
+      const int i = it.x0 + il;
+      const bool active = ly < G.LY && i < L.nx;
+      const Taps tp = make_taps(G, il, i, L.nx);
+      const int ja = it.yb * G.RB + ra;
+      const int jend = active ? min(L.ny, (it.yb + 1) * G.RB) : 0;
       const bool va = ja < jend, vb = ja + 1 < jend, pair = i + 1 < L.nx;
       const int nsteps = it.k1 - it.k0 + 2;
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;           // signed plane stride along the sweep
@@ -373,6 +405,9 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
                                                        const __grid_constant__ CUtensorMap tm_r,
                                                        const __grid_constant__ CUtensorMap tm_pold,
                                                        const __grid_constant__ CUtensorMap tm_pnew,
+                                                       const __grid_constant__ CUtensorMap tm_r_h,
+                                                       const __grid_constant__ CUtensorMap tm_pold_h,
+                                                       const __grid_constant__ CUtensorMap tm_pnew_h,
                                                        const __grid_constant__ BandGeo G,
                                                        const double* __restrict__ pold, double* __restrict__ pnew,
                                                        int newbuf) {
@@ -456,8 +491,9 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
       bool waited = false;
       for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
-        const int y0 = it.band * G.RB;
+        const int y0 = it.yb * G.RB;
         const int nsteps = it.k1 - it.k0 + 2;
+        const unsigned p_tx = (unsigned)(G.NBX * boxb + (G.ntx > 1 ? 2 * (G.RB + 2) * 16 : 0));
         for (int s = 0; s < nsteps; ++s, ++n) {
           const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
           const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
@@ -470,32 +506,35 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
           }
           const unsigned st = n % kStages, ph = (n / kStages) & 1u;
           mbar_wait(empty0 + 8 * st, ph ^ 1u);
-          mbar_expect_tx(full0 + 8 * st, (unsigned)(2 * G.p_bytes));
+          mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
           for (int b = 0; b < G.NBX; ++b) {
-            tma_load_3d(dst + b * boxb, ghost ? &tm_pnew : &tm_r, b * BW, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + b * boxb, &tm_pold, b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + b * boxb, ghost ? &tm_pnew : &tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + b * boxb, &tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+          }
+          if (G.ntx > 1) {
+            const int xl = it.x0 - 2, xr = it.x0 + 2 * G.LX;
+            tma_load_3d(dst + G.h_off, ghost ? &tm_pnew_h : &tm_r_h, xl, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.h_off + 128, ghost ? &tm_pnew_h : &tm_r_h, xr, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + G.h_off, &tm_pold_h, xl, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + G.h_off + 128, &tm_pold_h, xr, y0, q + 1, full0 + 8 * st);
           }
         }
       }
     }
   } else {
     const int lx = threadIdx.x % G.LX, ly = threadIdx.x / G.LX;
-    const int i = 2 * lx;
-    const bool active = ly < G.LY && i < L.nx;
+    const int il = 2 * lx;
     const int ra = 2 * ly;
-    const int bx = i / BW, col = i % BW;
-    Taps tp;
-    tp.c = bx * boxb + col * 8;
-    tp.l = i == 0 ? -1 : (col == 0 ? (bx - 1) * boxb + (BW - 1) * 8 : tp.c - 8);
-    tp.r = i + 2 >= L.nx ? -1 : (col + 2 == BW ? (bx + 1) * boxb : tp.c + 16);
-    const bool pair = i + 1 < L.nx;
     unsigned n = 0;
     for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
-      const int j0 = it.band * G.RB;
-      const int ja = j0 + ra;
-      const int jend = active ? min(L.ny, (it.band + 1) * G.RB) : 0;
+      const int i = it.x0 + il;
+      const bool active = ly < G.LY && i < L.nx;
+      const bool pair = i + 1 < L.nx;
+      const Taps tp = make_taps(G, il, i, L.nx);
+      const int ja = it.yb * G.RB + ra;
+      const int jend = active ? min(L.ny, (it.yb + 1) * G.RB) : 0;
       const bool va = ja < jend, vb = ja + 1 < jend;
       const int nsteps = it.k1 - it.k0 + 2;
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;
@@ -564,15 +603,19 @@ EncodeFn get_encode() {
 
 bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size_t* smem) {
   const cgb_layout_t& L = P.lay;
-  if (!kind_is_3d(P.st.kind) || L.nx > kMaxNx) return false;
+  if (!kind_is_3d(P.st.kind)) return false;
   BandGeo G{};
-  G.LX = (((L.nx + 1) / 2) + 31) / 32 * 32;
+  G.ntx = (L.nx + kTileX - 1) / kTileX;
+  const int tile = G.ntx > 1 ? kTileX : L.nx;       // rows wider than one tile are cut into 512-cell tiles
+  G.LX = (((tile + 1) / 2) + 31) / 32 * 32;
   G.LY = kNC / G.LX;
   if (G.LY > 8) G.LY = 8;  // keeps a slab <= 18 rows
   G.RB = 2 * G.LY;
-  G.NBX = (L.nx + BW - 1) / BW;
-  G.nbands = (L.ny + G.RB - 1) / G.RB;
-  G.p_bytes = G.NBX * (G.RB + 2) * BW * 8;
+  G.NBX = (tile + BW - 1) / BW;
+  G.nby = (L.ny + G.RB - 1) / G.RB;
+  G.nbands = G.ntx * G.nby;
+  G.h_off = G.NBX * (G.RB + 2) * BW * 8;              // halo boxes sit behind the main boxes
+  G.p_bytes = G.h_off + (G.ntx > 1 ? 256 : 0);
   G.xr_bytes = G.NBX * G.RB * BW * 8;
   G.stage_bytes = mode == kSpmvPUpdate ? 2 * G.p_bytes : G.p_bytes + (mode == kSpmvUpdate ? 2 * G.xr_bytes : 0);
   G.nstages = (int)((200 * 1024) / G.stage_bytes);
@@ -623,7 +666,8 @@ bool spmv_tma_supported(const RankDev& P) {
 }
 
 // halo_rows = 1: slabs of RB+2 rows (SpMV input); 0: exactly the band's RB rows (x / r of the update).
-int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows) {
+// box_cols = 128 for the main boxes, 2 for the x-halo boxes of tiled rows.
+int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows, int box_cols) {
   EncodeFn enc = get_encode();
   if (!enc) return fail(CGB_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   RankDev P{};
@@ -635,7 +679,7 @@ int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, i
   if (!make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm)) return fail(CGB_ERR_UNSUPPORTED, "layout not supported by the TMA SpMV");
   cuuint64_t dims[3] = {(cuuint64_t)L.nx, (cuuint64_t)L.py, (cuuint64_t)L.pz};
   cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.pitch * L.py * 8};
-  cuuint32_t box[3] = {BW, (cuuint32_t)(G.RB + (halo_rows ? 2 : 0)), 1};
+  cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)(G.RB + (halo_rows ? 2 : 0)), 1};
   cuuint32_t es[3] = {1, 1, 1};
   CUresult r = enc((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(vec), dims, strides,
                    box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -644,8 +688,8 @@ int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, i
   return CGB_OK;
 }
 
-cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_x, const void* map_r,
-                            double* out, int mode, cudaStream_t s) {
+cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_h, const void* map_x,
+                            const void* map_r, double* out, int mode, cudaStream_t s) {
   static bool attr_set[64] = {};
   if (device >= 0 && device < 64 && !attr_set[device]) {
     const int lim = 220 * 1024;
@@ -666,15 +710,17 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
   size_t sm;
   if (!make_geo(P, nsm, mode, &G, &grid, &sm)) return cudaErrorInvalidConfiguration;
   if (mode == kSpmvUpdate && (!map_x || !map_r)) return cudaErrorInvalidValue;
+  if (G.ntx > 1 && !map_h) return cudaErrorInvalidValue;
   const CUtensorMap& tm = *reinterpret_cast<const CUtensorMap*>(map);
+  const CUtensorMap& th = *reinterpret_cast<const CUtensorMap*>(map_h ? map_h : map);
   const CUtensorMap& tx = *reinterpret_cast<const CUtensorMap*>(map_x ? map_x : map);
   const CUtensorMap& tr = *reinterpret_cast<const CUtensorMap*>(map_r ? map_r : map);
   const bool k7 = P.st.kind == CGB_KIND_POISSON3D7;
   if (!k7 && P.st.kind != CGB_KIND_STENCIL3D27) return cudaErrorInvalidValue;
 #define CGB_TMA_LAUNCH(OUT)                                                                        \
   do {                                                                                             \
-    if (k7) k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, tx, tr, G, out, mode); \
-    else k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, tx, tr, G, out, mode);   \
+    if (k7) k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode); \
+    else k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);   \
   } while (0)
   if (mode == kSpmvUpdate) CGB_TMA_LAUNCH(2);
   else if (mode == kSpmvAlphaNoStore) CGB_TMA_LAUNCH(1);
@@ -683,8 +729,8 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
   return cudaGetLastError();
 }
 
-cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* map_r, const void* map_pold,
-                             const void* map_pnew, const double* pold, double* pnew, int newbuf, cudaStream_t s) {
+cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const maps[6], const double* pold, double* pnew,
+                             int newbuf, cudaStream_t s) {
   static bool attr_set[64] = {};
   if (device >= 0 && device < 64 && !attr_set[device]) {
     const auto at = cudaFuncAttributeMaxDynamicSharedMemorySize;
@@ -699,13 +745,13 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* map_r, co
   int grid;
   size_t sm;
   if (!make_geo(P, nsm, kSpmvPUpdate, &G, &grid, &sm)) return cudaErrorInvalidConfiguration;
-  const CUtensorMap& tr = *reinterpret_cast<const CUtensorMap*>(map_r);
-  const CUtensorMap& to = *reinterpret_cast<const CUtensorMap*>(map_pold);
-  const CUtensorMap& tn = *reinterpret_cast<const CUtensorMap*>(map_pnew);
+  // maps: r, p_old, p_new (main boxes), then their 2-column halo-box twins (used when rows are tiled)
+  const CUtensorMap* m[6];
+  for (int k = 0; k < 6; ++k) m[k] = reinterpret_cast<const CUtensorMap*>(maps[k] ? maps[k] : maps[k % 3]);
   if (P.st.kind == CGB_KIND_POISSON3D7)
-    k_pspmv_tma<CGB_KIND_POISSON3D7><<<grid, kNT, sm, s>>>(P, tr, to, tn, G, pold, pnew, newbuf);
+    k_pspmv_tma<CGB_KIND_POISSON3D7><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
   else if (P.st.kind == CGB_KIND_STENCIL3D27)
-    k_pspmv_tma<CGB_KIND_STENCIL3D27><<<grid, kNT, sm, s>>>(P, tr, to, tn, G, pold, pnew, newbuf);
+    k_pspmv_tma<CGB_KIND_STENCIL3D27><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
   else
     return cudaErrorInvalidValue;
   return cudaGetLastError();

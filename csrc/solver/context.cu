@@ -85,7 +85,10 @@ int alloc_common(cgb_ctx* c) {
     int r2 = spmv_tma_make_map(c->lay, P.x, c->tmap_x, 0);
     int r3 = spmv_tma_make_map(c->lay, P.r, c->tmap_r, 0);
     int r4 = spmv_tma_make_map(c->lay, P.r, c->tmap_rh, 1);
-    c->tma_ok = (r0 == CGB_OK && r1 == CGB_OK && r2 == CGB_OK && r3 == CGB_OK && r4 == CGB_OK);
+    int r5 = spmv_tma_make_map(c->lay, P.exch[0], c->tmap_h[0], 1, 2);
+    int r6 = spmv_tma_make_map(c->lay, P.exch[1], c->tmap_h[1], 1, 2);
+    int r7 = spmv_tma_make_map(c->lay, P.r, c->tmap_rh_h, 1, 2);
+    c->tma_ok = (r0 | r1 | r2 | r3 | r4 | r5 | r6 | r7) == CGB_OK;
   }
   // timeout for peer waits lives in the control block and survives solves
   Scalars init{};
@@ -447,7 +450,7 @@ static bool use_tma(const cgb_ctx* c) {
 static int enqueue_spmv(cgb_ctx* c, int buf, int mode, cudaStream_t s) {
   const RankDev& P = c->P;
   if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[buf], P.Ap, mode, s));
-  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[buf], nullptr, nullptr, P.Ap, mode, s));
+  else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[buf], c->tmap_h[buf], nullptr, nullptr, P.Ap, mode, s));
   else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[buf], P.Ap, mode, s));
   return CGB_OK;
 }
@@ -463,16 +466,17 @@ int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
   if (c->opts.variant == CGB_VAR_MERGED2) {
     // 64 B/DOF, two kernels: (p-update + SpMV + p.Ap) then (stencil again + x/r update + r.r)
     const int cur = c->host_cur, nb = cur ^ 1;
-    CGB_CUDA(launch_pspmv_tma(P, c->device, c->tmap_rh, c->tmap[cur], c->tmap[nb], P.exch[cur], P.exch[nb], nb, s));
-    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[nb], c->tmap_x, c->tmap_r, P.Ap, kSpmvUpdate, s));
+    const void* maps[6] = {c->tmap_rh, c->tmap[cur], c->tmap[nb], c->tmap_rh_h, c->tmap_h[cur], c->tmap_h[nb]};
+    CGB_CUDA(launch_pspmv_tma(P, c->device, maps, P.exch[cur], P.exch[nb], nb, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[nb], c->tmap_h[nb], c->tmap_x, c->tmap_r, P.Ap, kSpmvUpdate, s));
     c->host_cur = nb;
     return CGB_OK;
   }
   double* p = P.exch[0];
   if (c->opts.variant == CGB_VAR_MERGED) {
     // 72 B/DOF: Ap is never stored; the update kernel re-evaluates the stencil from the p slabs
-    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], nullptr, nullptr, P.Ap, kSpmvAlphaNoStore, s));
-    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_x, c->tmap_r, P.Ap, kSpmvUpdate, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_h[0], nullptr, nullptr, P.Ap, kSpmvAlphaNoStore, s));
+    CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_h[0], c->tmap_x, c->tmap_r, P.Ap, kSpmvUpdate, s));
     CGB_CUDA(launch_pupdate(P, c->cfg, p, 0, s));
     return CGB_OK;
   }
@@ -629,7 +633,7 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
     CGB_CUDA(launch_stage_x0(c->P, c->cfg, c->stream));
     const RankDev& P = c->P;
     if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.Ap, kSpmvPlain, c->stream));
-    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], nullptr, nullptr, P.Ap, kSpmvPlain, c->stream));
+    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_h[0], nullptr, nullptr, P.Ap, kSpmvPlain, c->stream));
     else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.Ap, kSpmvPlain, c->stream));
     c->launches += 2;
   }
@@ -642,7 +646,7 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
     // w0 = A r0 (r0 = b sits in exchange buffer 0 after k_init), then the first (gamma, delta)
     const RankDev& P = c->P;
     if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.exch[1], kSpmvPlain, c->stream));
-    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], nullptr, nullptr, P.exch[1], kSpmvPlain, c->stream));
+    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_h[0], nullptr, nullptr, P.exch[1], kSpmvPlain, c->stream));
     else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.exch[1], kSpmvPlain, c->stream));
     CGB_CUDA(launch_pipe_start(P, c->cfg, 1, c->stream));
     c->launches += 2;

@@ -55,6 +55,8 @@ struct cgb_ctx {
   alignas(64) unsigned char tmap_x[128] = {};   // band-row maps of x and r (update mode)
   alignas(64) unsigned char tmap_r[128] = {};
   alignas(64) unsigned char tmap_rh[128] = {};  // r with halo rows (merged variant)
+  alignas(64) unsigned char tmap_h[2][128] = {};  // 2-column x-halo boxes of exch[0], exch[1] (tiled rows)
+  alignas(64) unsigned char tmap_rh_h[128] = {};  // ... and of r
   bool tma_ok = false;
 
   ~cgb_ctx();

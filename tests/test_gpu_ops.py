@@ -10,6 +10,7 @@ PROBLEMS = [
     Problem.poisson2d(33, 17), Problem.poisson2d(1100, 70), Problem.poisson2d(512, 130),
     Problem.poisson3d(7, 5, 3), Problem.poisson3d(66, 19, 37), Problem.poisson3d(128, 64, 48),
     Problem.stencil27(9, 6, 5), Problem.stencil27(70, 21, 35), Problem.stencil27(64, 64, 40),
+    Problem.poisson3d(1030, 7, 5), Problem.stencil27(1537, 6, 4),      # rows wider than one 512-cell TMA tile
 ]
 
 

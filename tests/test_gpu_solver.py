@@ -229,3 +229,21 @@ def test_host_history_streams_every_residual_to_pinned_memory():
     hist.zero_()
     s.solve(tol=1e-8)
     assert float(hist.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("variant", ["fused", "recompute", "merged", "pipelined"])
+@pytest.mark.parametrize("prob", [Problem.poisson3d(1030, 9, 7), Problem.stencil27(1537, 6, 5)],
+                         ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
+def test_x_tiled_rows_all_variants(prob, variant):
+    # nx > 512: the TMA kernels cut rows into 512-cell tiles whose x halo arrives in 2-column boxes.
+    b = prob.rhs("random", seed=37)
+    ref = cpu_cg(prob, b, tol=1e-8, variant="pipelined" if variant == "pipelined" else "classic")
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-8, variant=variant, spmv="tma", chunk=5)
+    assert res.status == 1 and abs(res.iters - ref.iters) <= 2
+    n = min(res.iters, ref.iters)
+    h = s.history(n)
+    big = ref.history[:n] > 1e-5 * ref.r0norm
+    np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-5 if variant == "pipelined" else 1e-8)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
