@@ -82,8 +82,8 @@ extern "C" int cgb_op_spmv_stencil(const cgb_stencil_t* st, const cgb_layout_t* 
   if (impl == CGB_SPMV_TMA && !tma) return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV needs a 3D stencil problem");
   if (tma) {
     alignas(64) unsigned char map[128], map_h[128];
-    CGB_TRY(spmv_tma_make_map(*lay, p, map));
-    CGB_TRY(spmv_tma_make_map(*lay, p, map_h, 1, 2));
+    CGB_TRY(spmv_tma_make_map(st->kind, *lay, p, map));
+    CGB_TRY(spmv_tma_make_map(st->kind, *lay, p, map_h, 1, 2));
     int dev = 0;
     CGB_CUDA(cudaGetDevice(&dev));
     CGB_CUDA(launch_spmv_tma(P, dev, map, map_h, nullptr, nullptr, Ap, dot_out ? kSpmvDot : kSpmvPlain, s));

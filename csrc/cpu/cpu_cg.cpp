@@ -27,7 +27,7 @@ struct CpuRank {
 
 double local_spmv(const cgb_stencil_t& st, const cgb_layout_t& L, const double* in, double* out,
                   const double* dot_with) {
-  const int zr = kind_is_3d(st.kind) ? 1 : 0;
+  const int zr = kind_has_z_taps(st.kind) ? 1 : 0;
   struct Tap { int dx; int64_t off; double c; };
   std::vector<Tap> taps;
   for (int dz = -zr; dz <= zr; ++dz)

@@ -219,7 +219,7 @@ __device__ __forceinline__ void plane_full(const double* __restrict__ in, int64_
   const double xp = has_r ? in[idx + 2] : 0.0;
   o.s0[0] = c.x;
   o.s0[1] = c.y;
-  if (KIND == CGB_KIND_POISSON2D5) {  // marching axis is y: only the x neighbours are in-plane
+  if (KIND == CGB_KIND_POISSON2D5) {  // one row per plane: only the x neighbours are in-plane
     o.s1[0] = xm + c.y;
     o.s1[1] = c.x + xp;
     return;
@@ -249,11 +249,11 @@ __global__ void __launch_bounds__(kThreads) k_spmv(const __grid_constant__ RankD
   const int lx = k2d ? threadIdx.x : (threadIdx.x & 31);
   const int ly = k2d ? 0 : (threadIdx.x >> 5);
   const int pitch = L.pitch;
-  const int64_t ms = k2d ? (int64_t)pitch : (int64_t)pitch * L.py;
-  const int mext = k2d ? L.ny : L.nz;
+  const int64_t ms = (int64_t)pitch * L.py;
+  const int mext = L.nz;
   const double cc = P.st.c_center, cf = P.st.c_face, ce = P.st.c_edge, cn = P.st.c_corner;
   const int nitems = P.ntx * P.nty * P.nmc;
-  const int mlo = dir_index(k2d ? -1 : 0, k2d ? 0 : -1), mhi = dir_index(k2d ? 1 : 0, k2d ? 0 : 1);
+  const int mlo = dir_index(0, -1), mhi = dir_index(0, 1);
   const bool nb_mlo = P.nbr[mlo] >= 0, nb_mhi = P.nbr[mhi] >= 0;
   const bool nb_ylo = !k2d && P.nbr[dir_index(-1, 0)] >= 0, nb_yhi = !k2d && P.nbr[dir_index(1, 0)] >= 0;
   double acc = 0.0;
@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(kThreads) k_spmv(const __grid_constant__ RankD
       const int j = ty_t * TY + ly;
       if (i >= L.nx || (!k2d && j >= L.ny)) continue;
       const int m0 = mc * P.mchunk, m1 = min(mext, m0 + P.mchunk);
-      int64_t idx = k2d ? lay_index(L, i, m0 - 1, 0) : lay_index(L, i, j, m0 - 1);
+      int64_t idx = lay_index(L, i, j, m0 - 1);
       PS prev, cur, next;
       if (KIND == CGB_KIND_STENCIL3D27) plane_full<KIND>(in, idx, i, L.nx, pitch, prev);
       else plane_center<KIND>(in, idx, prev);
@@ -549,7 +549,7 @@ void choose_spmv_tiling(RankDev& P, int grid_spmv) {
   if (P.st.kind == CGB_KIND_POISSON2D5) {
     P.ntx = (L.nx + 2 * kThreads - 1) / (2 * kThreads);
     P.nty = 1;
-    int ext = L.ny, mc = 32;
+    int ext = L.nz, mc = 32;
     while (mc > 4 && (long long)P.ntx * ((ext + mc - 1) / mc) < 2LL * grid_spmv) mc >>= 1;
     P.mchunk = mc;
     P.nmc = (ext + mc - 1) / mc;

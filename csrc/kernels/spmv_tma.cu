@@ -40,11 +40,14 @@ constexpr int BW = 128;                  // cells per TMA box row
 constexpr int kNC = 512;                 // consumer threads
 constexpr int kNT = kNC + 32;            // + one producer warp
 constexpr int kMaxStages = 8;
-constexpr int kTileX = 512;             // cells per x tile when the row is wider than one tile
+constexpr int kTileX3 = 512;            // cells per x tile when a 3D row is wider than one tile (2 rows/thread)
+constexpr int kTileX2 = 1024;           // ... and for 2D grids (1 row/thread)
 
 struct BandGeo {
   int LX, LY;        // consumer thread grid: LX pair-columns x LY row-pairs
-  int RB;            // rows per band = 2*LY
+  int RB;            // rows per band = 2*LY (1 for 2D grids: one row per plane)
+  int HY;            // halo rows above/below a band in a p slab: 1, or 0 for 2D grids (no y taps)
+  int prow;          // rows of a p slab = RB + 2*HY
   int NBX;           // 128-wide TMA boxes per slab row
   int ntx, nby;      // x tiles (of 2*LX cells) and row bands; nbands = ntx*nby
   int h_off;         // x-tiled layouts: byte offset of the two 2-column halo boxes inside a p slab
@@ -103,7 +106,7 @@ struct Taps {
 // Offsets of a consumer thread's taps. il = x offset inside the tile, i = global x.
 __device__ __forceinline__ Taps make_taps(const BandGeo& G, int il, int i, int nx) {
   constexpr int RS = BW * 8;
-  const int boxb = (G.RB + 2) * RS;
+  const int boxb = G.prow * RS;
   const int b = il / BW, col = il % BW;
   Taps tp;
   tp.c = b * boxb + col * 8;
@@ -133,6 +136,15 @@ __device__ __forceinline__ void plane_from_slab(const unsigned char* slab, const
   auto ld2 = [&](int row) { return *reinterpret_cast<const double2*>(b0 + row * RS + tp.c); };
   auto ldl = [&](int row) { return tp.l >= 0 ? *reinterpret_cast<const double*>(slab + tp.l + (ra + row) * tp.ls) : 0.0; };
   auto ldr = [&](int row) { return tp.r >= 0 ? *reinterpret_cast<const double*>(slab + tp.r + (ra + row) * tp.rs) : 0.0; };
+  if (KIND == CGB_KIND_POISSON2D5) {  // one row per plane, no halo rows: slab row 0 is the thread's row
+    const double2 c = ld2(0);
+    const double l = ldl(0), q = ldr(0);
+    A.s0[0] = c.x; A.s0[1] = c.y;
+    A.s1[0] = l + c.y;
+    A.s1[1] = c.x + q;
+    B = A;
+    return;
+  }
   const double2 c0 = ld2(0), c1 = ld2(1), c2 = ld2(2), c3 = ld2(3);
   const double l1 = ldl(1), q1 = ldr(1), l2 = ldl(2), q2 = ldr(2);
   A.s0[0] = c1.x; A.s0[1] = c1.y;
@@ -176,6 +188,16 @@ __device__ __forceinline__ void plane_from_two(const unsigned char* rslab, const
     const int o = tp.r + (ra + row) * tp.rs;
     return tp.r >= 0 ? *reinterpret_cast<const double*>(rslab + o) + bt * *reinterpret_cast<const double*>(pslab + o) : 0.0;
   };
+  if (KIND == CGB_KIND_POISSON2D5) {
+    const double2 c = pn2(0);
+    const double l = pnl(0), q = pnr(0);
+    pna = pnb = c;
+    A.s0[0] = c.x; A.s0[1] = c.y;
+    A.s1[0] = l + c.y;
+    A.s1[1] = c.x + q;
+    B = A;
+    return;
+  }
   const double2 c0 = pn2(0), c1 = pn2(1), c2 = pn2(2), c3 = pn2(3);
   const double l1 = pnl(1), q1 = pnr(1), l2 = pnl(2), q2 = pnr(2);
   pna = c1;
@@ -301,7 +323,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
         if (it.y_ghost) wait_flags();
         const int y0 = it.yb * G.RB;  // padded row of band row -1
         const int nsteps = it.k1 - it.k0 + 2;
-        const unsigned p_tx = (unsigned)(G.NBX * (G.RB + 2) * BW * 8 + (G.ntx > 1 ? 2 * (G.RB + 2) * 16 : 0));
+        const unsigned p_tx = (unsigned)(G.NBX * G.prow * BW * 8 + (G.ntx > 1 ? 2 * G.prow * 16 : 0));
         for (int s = 0; s < nsteps; ++s, ++n) {
           const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
           if ((q == -1 && nb_zlo) || (q == L.nz && nb_zhi)) wait_flags();
@@ -311,7 +333,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
           mbar_expect_tx(full0 + 8 * st, p_tx + (with_xr ? 2u * (unsigned)G.xr_bytes : 0u));
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
           for (int b = 0; b < G.NBX; ++b)
-            tma_load_3d(dst + b * (G.RB + 2) * BW * 8, &tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + b * G.prow * BW * 8, &tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
           if (G.ntx > 1) {  // the tile's x halo: two 2-column boxes (zero-filled outside the domain)
             tma_load_3d(dst + G.h_off, &tmap_h, it.x0 - 2, y0, q + 1, full0 + 8 * st);
             tma_load_3d(dst + G.h_off + 128, &tmap_h, it.x0 + 2 * G.LX, y0, q + 1, full0 + 8 * st);
@@ -319,8 +341,8 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
           if (with_xr) {
             const int ko = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
             for (int b = 0; b < G.NBX; ++b) {
-              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, &tmx, it.x0 + b * BW, y0 + 1, ko + 1, full0 + 8 * st);
-              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, &tmr, it.x0 + b * BW, y0 + 1, ko + 1,
+              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, &tmx, it.x0 + b * BW, y0 + G.HY, ko + 1, full0 + 8 * st);
+              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, &tmr, it.x0 + b * BW, y0 + G.HY, ko + 1,
                           full0 + 8 * st);
             }
           }
@@ -356,9 +378,11 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
         if (OUT == 2 && s >= 2 && active) {  // x and r rows of the plane emitted now (TMA-staged)
           const unsigned char* xs = stage + G.p_bytes + xr_off;
           cxa = *reinterpret_cast<const double2*>(xs);
-          cxb = *reinterpret_cast<const double2*>(xs + BW * 8);
           cra = *reinterpret_cast<const double2*>(xs + G.xr_bytes);
-          crb = *reinterpret_cast<const double2*>(xs + G.xr_bytes + BW * 8);
+          if (KIND != CGB_KIND_POISSON2D5) {
+            cxb = *reinterpret_cast<const double2*>(xs + BW * 8);
+            crb = *reinterpret_cast<const double2*>(xs + G.xr_bytes + BW * 8);
+          }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
@@ -482,7 +506,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
   }
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int boxb = (G.RB + 2) * BW * 8;
+  const int boxb = G.prow * BW * 8;
   double acc = 0.0;
 
   if (warp == kNC / 32) {
@@ -493,7 +517,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
         const int y0 = it.yb * G.RB;
         const int nsteps = it.k1 - it.k0 + 2;
-        const unsigned p_tx = (unsigned)(G.NBX * boxb + (G.ntx > 1 ? 2 * (G.RB + 2) * 16 : 0));
+        const unsigned p_tx = (unsigned)(G.NBX * boxb + (G.ntx > 1 ? 2 * G.prow * 16 : 0));
         for (int s = 0; s < nsteps; ++s, ++n) {
           const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
           const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
@@ -603,23 +627,28 @@ EncodeFn get_encode() {
 
 bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size_t* smem) {
   const cgb_layout_t& L = P.lay;
-  if (!kind_is_3d(P.st.kind)) return false;
+  if (!kind_is_stencil(P.st.kind)) return false;
   BandGeo G{};
-  G.ntx = (L.nx + kTileX - 1) / kTileX;
-  const int tile = G.ntx > 1 ? kTileX : L.nx;       // rows wider than one tile are cut into 512-cell tiles
+  const bool flat = !kind_has_y_taps(P.st.kind);      // 2D grid stored as nx x 1 x ny
+  const int tile_max = flat ? kTileX2 : kTileX3;
+  G.ntx = (L.nx + tile_max - 1) / tile_max;
+  const int tile = G.ntx > 1 ? tile_max : L.nx;     // wide rows are cut into tiles
   G.LX = (((tile + 1) / 2) + 31) / 32 * 32;
-  G.LY = kNC / G.LX;
+  G.LY = flat ? 1 : kNC / G.LX;
   if (G.LY > 8) G.LY = 8;  // keeps a slab <= 18 rows
-  G.RB = 2 * G.LY;
+  G.RB = flat ? 1 : 2 * G.LY;
+  G.HY = flat ? 0 : 1;
+  G.prow = G.RB + 2 * G.HY;
   G.NBX = (tile + BW - 1) / BW;
   G.nby = (L.ny + G.RB - 1) / G.RB;
   G.nbands = G.ntx * G.nby;
-  G.h_off = G.NBX * (G.RB + 2) * BW * 8;              // halo boxes sit behind the main boxes
+  G.h_off = G.NBX * G.prow * BW * 8;                  // halo boxes sit behind the main boxes
   G.p_bytes = G.h_off + (G.ntx > 1 ? 256 : 0);
   G.xr_bytes = G.NBX * G.RB * BW * 8;
   G.stage_bytes = mode == kSpmvPUpdate ? 2 * G.p_bytes : G.p_bytes + (mode == kSpmvUpdate ? 2 * G.xr_bytes : 0);
   G.nstages = (int)((200 * 1024) / G.stage_bytes);
-  const int cap = mode == kSpmvAlpha || mode == kSpmvDot || mode == kSpmvPlain || mode == kSpmvAlphaNoStore ? 6 : 4;
+  const int cap = flat ? kMaxStages
+                       : (mode == kSpmvAlpha || mode == kSpmvDot || mode == kSpmvPlain || mode == kSpmvAlphaNoStore ? 6 : 4);
   if (G.nstages > cap) G.nstages = cap;
   if (G.nstages < 2) return false;
   const size_t sm = (size_t)G.nstages * G.stage_bytes;
@@ -667,19 +696,19 @@ bool spmv_tma_supported(const RankDev& P) {
 
 // halo_rows = 1: slabs of RB+2 rows (SpMV input); 0: exactly the band's RB rows (x / r of the update).
 // box_cols = 128 for the main boxes, 2 for the x-halo boxes of tiled rows.
-int spmv_tma_make_map(const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows, int box_cols) {
+int spmv_tma_make_map(int kind, const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows, int box_cols) {
   EncodeFn enc = get_encode();
   if (!enc) return fail(CGB_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
   RankDev P{};
   P.lay = L;
-  P.st.kind = CGB_KIND_POISSON3D7;
+  P.st.kind = kind;
   BandGeo G;
   int grid;
   size_t sm;
   if (!make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm)) return fail(CGB_ERR_UNSUPPORTED, "layout not supported by the TMA SpMV");
   cuuint64_t dims[3] = {(cuuint64_t)L.nx, (cuuint64_t)L.py, (cuuint64_t)L.pz};
   cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.pitch * L.py * 8};
-  cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)(G.RB + (halo_rows ? 2 : 0)), 1};
+  cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)(halo_rows ? G.prow : G.RB), 1};
   cuuint32_t es[3] = {1, 1, 1};
   CUresult r = enc((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(vec), dims, strides,
                    box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -700,6 +729,9 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27, 0>, at, lim);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27, 1>, at, lim);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_STENCIL3D27, 2>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON2D5, 0>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON2D5, 1>, at, lim);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_spmv_tma<CGB_KIND_POISSON2D5, 2>, at, lim);
     if (e != cudaSuccess) return e;
     attr_set[device] = true;
   }
@@ -715,12 +747,16 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
   const CUtensorMap& th = *reinterpret_cast<const CUtensorMap*>(map_h ? map_h : map);
   const CUtensorMap& tx = *reinterpret_cast<const CUtensorMap*>(map_x ? map_x : map);
   const CUtensorMap& tr = *reinterpret_cast<const CUtensorMap*>(map_r ? map_r : map);
-  const bool k7 = P.st.kind == CGB_KIND_POISSON3D7;
-  if (!k7 && P.st.kind != CGB_KIND_STENCIL3D27) return cudaErrorInvalidValue;
-#define CGB_TMA_LAUNCH(OUT)                                                                        \
-  do {                                                                                             \
-    if (k7) k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode); \
-    else k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);   \
+  const int kd = P.st.kind;
+  if (!kind_is_stencil(kd)) return cudaErrorInvalidValue;
+#define CGB_TMA_LAUNCH(OUT)                                                                                   \
+  do {                                                                                                        \
+    if (kd == CGB_KIND_POISSON3D7)                                                                            \
+      k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);            \
+    else if (kd == CGB_KIND_STENCIL3D27)                                                                      \
+      k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);           \
+    else                                                                                                      \
+      k_spmv_tma<CGB_KIND_POISSON2D5, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);            \
   } while (0)
   if (mode == kSpmvUpdate) CGB_TMA_LAUNCH(2);
   else if (mode == kSpmvAlphaNoStore) CGB_TMA_LAUNCH(1);
@@ -736,6 +772,7 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const map
     const auto at = cudaFuncAttributeMaxDynamicSharedMemorySize;
     cudaError_t e = cudaFuncSetAttribute(k_pspmv_tma<CGB_KIND_POISSON3D7>, at, 220 * 1024);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pspmv_tma<CGB_KIND_STENCIL3D27>, at, 220 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_pspmv_tma<CGB_KIND_POISSON2D5>, at, 220 * 1024);
     if (e != cudaSuccess) return e;
     attr_set[device] = true;
   }
@@ -752,6 +789,8 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const map
     k_pspmv_tma<CGB_KIND_POISSON3D7><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
   else if (P.st.kind == CGB_KIND_STENCIL3D27)
     k_pspmv_tma<CGB_KIND_STENCIL3D27><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
+  else if (P.st.kind == CGB_KIND_POISSON2D5)
+    k_pspmv_tma<CGB_KIND_POISSON2D5><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
   else
     return cudaErrorInvalidValue;
   return cudaGetLastError();

@@ -12,7 +12,14 @@ extern "C" int cgb_stencil_default(int kind, int gx, int gy, int gz, cgb_stencil
   CGB_REQUIRE(out != nullptr, "cgb_stencil_default: out is NULL");
   CGB_REQUIRE(kind >= CGB_KIND_CSR && kind <= CGB_KIND_STENCIL3D27, "unknown problem kind %d", kind);
   CGB_REQUIRE(gx >= 1 && gy >= 1 && gz >= 1, "grid extents must be >= 1 (got %d,%d,%d)", gx, gy, gz);
-  if (kind == CGB_KIND_POISSON2D5) CGB_REQUIRE(gz == 1, "2D problem needs gz == 1");
+  if (kind == CGB_KIND_POISSON2D5) {
+    // stored as nx x 1 x ny (see stencil.hpp); (nx, ny, 1) is accepted and rearranged
+    if (gz == 1 && gy > 1) {
+      gz = gy;
+      gy = 1;
+    }
+    CGB_REQUIRE(gy == 1, "2D problem: pass (nx, ny, 1) or (nx, 1, ny)");
+  }
   if (kind == CGB_KIND_CSR) CGB_REQUIRE(gy == 1 && gz == 1, "CSR problem is 1D: gy == gz == 1");
   cgb_stencil_t s{};
   s.kind = kind;
@@ -35,7 +42,7 @@ void for_each_entry(const cgb_stencil_t& st, int64_t row, F&& f) {
   int i = (int)(row % st.gx);
   int j = (int)((row / st.gx) % st.gy);
   int k = (int)(row / ((int64_t)st.gx * st.gy));
-  int zr = kind_is_3d(st.kind) ? 1 : 0;
+  int zr = kind_has_z_taps(st.kind) ? 1 : 0;
   for (int dz = -zr; dz <= zr; ++dz)
     for (int dy = -1; dy <= 1; ++dy)
       for (int dx = -1; dx <= 1; ++dx) {

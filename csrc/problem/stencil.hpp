@@ -15,15 +15,19 @@
 
 namespace cgb {
 
+// A 2D grid nx x ny is stored as nx x 1 x ny: one row per plane. It then shares everything with the
+// 3D problems (z-slab decomposition = row blocks, ghost planes, kernels); it simply has no y taps.
 CGB_HD bool kind_is_3d(int kind) { return kind == CGB_KIND_POISSON3D7 || kind == CGB_KIND_STENCIL3D27; }
 CGB_HD bool kind_is_stencil(int kind) { return kind != CGB_KIND_CSR; }
+CGB_HD bool kind_has_y_taps(int kind) { return kind_is_3d(kind); }
+CGB_HD bool kind_has_z_taps(int kind) { return kind_is_stencil(kind); }
 
 // Coefficient for an offset (dx,dy,dz) in {-1,0,1}^3; 0.0 if the offset is not part of the stencil.
 CGB_HD double stencil_coeff(const cgb_stencil_t& st, int dx, int dy, int dz) {
   int m = (dx != 0) + (dy != 0) + (dz != 0);
   if (m == 0) return st.c_center;
   if (m == 1) {
-    if (st.kind == CGB_KIND_POISSON2D5 && dz != 0) return 0.0;
+    if (st.kind == CGB_KIND_POISSON2D5 && dy != 0) return 0.0;
     return st.c_face;
   }
   if (st.kind != CGB_KIND_STENCIL3D27) return 0.0;
@@ -55,7 +59,7 @@ CGB_HD double manufactured_u(const cgb_stencil_t& st, int i, int j, int k) {
 // b = A u_manufactured evaluated with the stencil (zero Dirichlet outside the grid).
 CGB_HD double manufactured_b(const cgb_stencil_t& st, int i, int j, int k) {
   double s = 0.0;
-  int zr = kind_is_3d(st.kind) ? 1 : 0;
+  int zr = kind_has_z_taps(st.kind) ? 1 : 0;
   for (int dz = -zr; dz <= zr; ++dz)
     for (int dy = -1; dy <= 1; ++dy)
       for (int dx = -1; dx <= 1; ++dx) {

@@ -80,14 +80,14 @@ int alloc_common(cgb_ctx* c) {
   if (c->st.kind != CGB_KIND_CSR) choose_spmv_tiling(P, c->cfg.grid_spmv);
   c->tma_ok = false;
   if (spmv_tma_supported(P)) {
-    int r0 = spmv_tma_make_map(c->lay, P.exch[0], c->tmap[0]);
-    int r1 = spmv_tma_make_map(c->lay, P.exch[1], c->tmap[1]);
-    int r2 = spmv_tma_make_map(c->lay, P.x, c->tmap_x, 0);
-    int r3 = spmv_tma_make_map(c->lay, P.r, c->tmap_r, 0);
-    int r4 = spmv_tma_make_map(c->lay, P.r, c->tmap_rh, 1);
-    int r5 = spmv_tma_make_map(c->lay, P.exch[0], c->tmap_h[0], 1, 2);
-    int r6 = spmv_tma_make_map(c->lay, P.exch[1], c->tmap_h[1], 1, 2);
-    int r7 = spmv_tma_make_map(c->lay, P.r, c->tmap_rh_h, 1, 2);
+    int r0 = spmv_tma_make_map(c->st.kind, c->lay, P.exch[0], c->tmap[0]);
+    int r1 = spmv_tma_make_map(c->st.kind, c->lay, P.exch[1], c->tmap[1]);
+    int r2 = spmv_tma_make_map(c->st.kind, c->lay, P.x, c->tmap_x, 0);
+    int r3 = spmv_tma_make_map(c->st.kind, c->lay, P.r, c->tmap_r, 0);
+    int r4 = spmv_tma_make_map(c->st.kind, c->lay, P.r, c->tmap_rh, 1);
+    int r5 = spmv_tma_make_map(c->st.kind, c->lay, P.exch[0], c->tmap_h[0], 1, 2);
+    int r6 = spmv_tma_make_map(c->st.kind, c->lay, P.exch[1], c->tmap_h[1], 1, 2);
+    int r7 = spmv_tma_make_map(c->st.kind, c->lay, P.r, c->tmap_rh_h, 1, 2);
     c->tma_ok = (r0 | r1 | r2 | r3 | r4 | r5 | r6 | r7) == CGB_OK;
   }
   // timeout for peer waits lives in the control block and survives solves
@@ -444,7 +444,7 @@ static int launches_per_iter(const cgb_ctx* c) {
 static bool use_tma(const cgb_ctx* c) {
   if (!c->tma_ok || c->opts.spmv_impl == CGB_SPMV_SIMPLE) return false;
   if (c->opts.spmv_impl == CGB_SPMV_TMA) return true;
-  return c->st.kind == CGB_KIND_POISSON3D7;
+  return c->st.kind == CGB_KIND_POISSON3D7 || c->st.kind == CGB_KIND_POISSON2D5;
 }
 
 static int enqueue_spmv(cgb_ctx* c, int buf, int mode, cudaStream_t s) {
@@ -588,7 +588,8 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   c->opts = *o;
   if (c->opts.variant == CGB_VAR_AUTO) {
     // measured on B200 (profiles/): for the 7-point stencil merged > recompute > fused; 27-point stays fused
-    const bool tma7 = c->tma_ok && c->st.kind == CGB_KIND_POISSON3D7 && o->spmv_impl != CGB_SPMV_SIMPLE;
+    const bool tma7 = c->tma_ok && (c->st.kind == CGB_KIND_POISSON3D7 || c->st.kind == CGB_KIND_POISSON2D5) &&
+                      o->spmv_impl != CGB_SPMV_SIMPLE;
     c->opts.variant = !tma7 ? CGB_VAR_FUSED : (merged2_ok(c) ? CGB_VAR_MERGED2 : CGB_VAR_MERGED);
   }
   if (c->opts.chunk < 1) c->opts.chunk = 25;

@@ -16,10 +16,11 @@ int make_partition(const cgb_stencil_t& st, int nranks, int rank, int decomp, in
     CGB_REQUIRE(nranks == 1, "general CSR problems are single-rank (multi-GPU CSR is not implemented)");
     Py = Pz = 1;
   } else if (!is3d) {
-    CGB_REQUIRE(Pz == 0 || Pz == 1, "2D problems are split along y only");
-    Pz = 1;
-    CGB_REQUIRE(Py == 0 || Py == nranks, "2D problems need Py == nranks");
-    Py = nranks;
+    // 2D grids are nx x 1 x ny: only the row (z) direction can be split
+    CGB_REQUIRE(Py == 0 || Py == 1, "2D problems are split along their rows only");
+    CGB_REQUIRE(Pz == 0 || Pz == nranks, "2D problems need Pz == nranks");
+    Py = 1;
+    Pz = nranks;
   } else if (Py == 0 && Pz == 0) {
     if (decomp == 2) {
       Py = 1;
@@ -66,8 +67,8 @@ int make_layout(const cgb_stencil_t& st, const cgb_partition_t& part, cgb_layout
   L.nx = part.nx;
   L.ny = part.ny;
   L.nz = part.nz;
-  L.gy = kind_is_stencil(st.kind) ? 1 : 0;
-  L.gz = kind_is_3d(st.kind) ? 1 : 0;
+  L.gy = kind_has_y_taps(st.kind) ? 1 : 0;
+  L.gz = kind_has_z_taps(st.kind) ? 1 : 0;
   L.pitch = (L.nx + 15) / 16 * 16;
   L.py = L.ny + 2 * L.gy;
   L.pz = L.nz + 2 * L.gz;

@@ -37,6 +37,8 @@ class Problem:
 
     @classmethod
     def poisson2d(cls, nx: int, ny: Optional[int] = None) -> "Problem":
+        """2D 5-point Poisson on an nx x ny grid. Internally the grid is nx x 1 x ny (one row per plane), so
+        ``dims`` reports (nx, 1, ny) and the row-block decomposition is the z-slab decomposition."""
         ny = nx if ny is None else ny
         return cls("poisson2d5", cls._stencil(N.KIND_POISSON2D5, nx, ny, 1))
 

@@ -45,14 +45,14 @@ typedef enum cgb_status {
 
 typedef enum cgb_kind {
   CGB_KIND_CSR = 0,        /* general CSR, fp64 values, int32 indices (CUDACG.cu:213-216) */
-  CGB_KIND_POISSON2D5 = 1, /* 2D 5-point, homogeneous Dirichlet */
+  CGB_KIND_POISSON2D5 = 1, /* 2D 5-point, homogeneous Dirichlet; the nx x ny grid is stored as nx x 1 x ny */
   CGB_KIND_POISSON3D7 = 2, /* 3D 7-point */
   CGB_KIND_STENCIL3D27 = 3 /* 3D 27-point */
 } cgb_kind;
 
 typedef struct cgb_stencil_t {
   int32_t kind;         /* cgb_kind */
-  int32_t gx, gy, gz;   /* global grid (gz = 1 for 2D; gx = n, gy = gz = 1 for CSR) */
+  int32_t gx, gy, gz;   /* global grid (2D: gy = 1 and the rows are in gz; CSR: gx = n, gy = gz = 1) */
   double c_center;      /* diagonal coefficient */
   double c_face;        /* neighbours sharing a face */
   double c_edge;        /* 27-pt only: neighbours sharing an edge */
@@ -93,8 +93,8 @@ typedef struct cgb_partition_t {
   int32_t nbr[CGB_NDIR]; /* neighbour rank per direction, -1 if none/not needed by the stencil */
 } cgb_partition_t;
 
-/* Py,Pz == 0 picks: 2D problems Py=nranks; 3D problems decomp=1 -> z slabs, decomp=2 -> the
- * most square Py x Pz factorisation. */
+/* Py,Pz == 0 picks: decomp=1 -> z slabs (row blocks for 2D grids), decomp=2 (3D only) -> the most square
+ * Py x Pz factorisation. */
 int cgb_partition_make(const cgb_stencil_t* st, int nranks, int rank, int decomp, int Py, int Pz,
                        cgb_partition_t* out);
 

@@ -11,6 +11,7 @@ PROBLEMS = [
     Problem.poisson3d(7, 5, 3), Problem.poisson3d(66, 19, 37), Problem.poisson3d(128, 64, 48),
     Problem.stencil27(9, 6, 5), Problem.stencil27(70, 21, 35), Problem.stencil27(64, 64, 40),
     Problem.poisson3d(1030, 7, 5), Problem.stencil27(1537, 6, 4),      # rows wider than one 512-cell TMA tile
+    Problem.poisson2d(2300, 9),                                        # 2D rows wider than one 1024-cell tile
 ]
 
 
@@ -22,8 +23,6 @@ def _setup(prob):
 @pytest.mark.parametrize("impl", ["simple", "tma"])
 @pytest.mark.parametrize("prob", PROBLEMS, ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
 def test_spmv_stencil_matches_oracle(prob, impl):
-    if impl == "tma" and prob.dims[2] == 1:
-        pytest.skip("TMA SpMV covers the 3D stencils")
     import torch
     from cuda_mpi_parallel_b200 import ops
     _, lay = _setup(prob)

@@ -134,10 +134,12 @@ def test_recompute_variant_matches_oracle(prob):
     assert rf.iters == res.iters
 
 
-def test_recompute_variant_rejects_unsupported_shapes():
+def test_recompute_variant_rejects_unsupported_problems():
     from cuda_mpi_parallel_b200._native import NativeError
-    s = CGSolver(Problem.poisson2d(64, 64))
-    s.set_rhs("ones")
+    p = Problem.poisson2d(12, 10)
+    rowptr, colind, val = p.to_csr()
+    s = CGSolver(Problem.csr(rowptr, colind, val))      # general CSR has no TMA path
+    s.set_rhs(np.ones(p.n))
     with pytest.raises(NativeError):
         s.solve(variant="recompute")
 
@@ -247,3 +249,21 @@ def test_x_tiled_rows_all_variants(prob, variant):
     big = ref.history[:n] > 1e-5 * ref.r0norm
     np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-5 if variant == "pipelined" else 1e-8)
     np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
+
+
+@pytest.mark.parametrize("variant", ["fused", "recompute", "merged", "pipelined"])
+@pytest.mark.parametrize("prob", [Problem.poisson2d(200, 90), Problem.poisson2d(33, 17), Problem.poisson2d(2300, 12)],
+                         ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
+def test_2d_problems_on_the_tma_kernels(prob, variant):
+    # a 2D grid is a one-row-per-plane 3D grid: same band kernels, no y taps
+    b = prob.rhs("random", seed=41)
+    ref = cpu_cg(prob, b, tol=1e-8, variant="pipelined" if variant == "pipelined" else "classic")
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-8, variant=variant, spmv="tma", chunk=5)
+    assert res.status == 1 and abs(res.iters - ref.iters) <= 2
+    n = min(res.iters, ref.iters)
+    h = s.history(n)
+    big = ref.history[:n] > 1e-5 * ref.r0norm
+    np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-5 if variant == "pipelined" else 1e-8)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6 * max(1.0, np.abs(ref.x).max()))

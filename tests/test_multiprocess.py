@@ -78,7 +78,7 @@ def test_gpu_fabric_recompute_variant(name, dims, decomp):
 @pytest.mark.gpu
 @pytest.mark.multigpu
 @pytest.mark.parametrize("name,dims", [("poisson3d7", "64x48x40"), ("stencil3d27", "36x42x38"), ("poisson3d7", "512x20x9"),
-                                       ("poisson3d7", "1030x6x12")])
+                                       ("poisson3d7", "1030x6x12"), ("poisson2d5", "300x40")])
 def test_gpu_fabric_merged_variant(name, dims):
     n = _ngpu()
     if n < 2:

@@ -211,6 +211,9 @@ int main(int argc, char** argv) {
     int nx = a.n[0] ? a.n[0] : 64, ny = a.n[1] ? a.n[1] : nx, nz = kind == CGB_KIND_POISSON2D5 ? 1 : (a.n[2] ? a.n[2] : nx);
     cgb_stencil_t st;
     check(cgb_stencil_default(kind, nx, ny, nz, &st), "problem setup");
+    nx = st.gx;  // 2D grids come back as nx x 1 x ny
+    ny = st.gy;
+    nz = st.gz;
     n_total = (long long)nx * ny * nz;
     const int rk = rhs_kind(a.rhs);
     hist.assign((size_t)a.maxit + 2, 0.0);
