@@ -74,8 +74,10 @@ def test_maxit_and_fixed_iters_and_rel_tolerance():
     s.set_rhs("ones")
     r = s.solve(tol=1e-14, maxit=10)
     assert r.status == 2 and r.iters == 10
-    r = s.solve(fixed_iters=33, chunk=10)
+    r = s.solve(fixed_iters=33, chunk=10, variant="fused")
     assert r.iters == 33 and r.launches == 1 + 3 * 33
+    r = s.solve(fixed_iters=33, chunk=10, variant="merged")
+    assert r.iters == 33 and r.launches == 1 + 2 * 33
     r = s.solve(tol=1e-6, tol_mode="rel", maxit=5000)
     assert r.status == 1 and r.rnorm < 1e-6 * r.r0norm
 
