@@ -36,7 +36,10 @@ namespace cgb {
 
 namespace {
 
-constexpr int BW = 128;                  // cells per TMA box row
+// cells per TMA box row: 128 for 3D problems; 256 for 2D grids, whose one-row slabs would otherwise
+// need five times as many TMA instructions per output as the 3D bands
+template <int KIND> struct BoxW { static constexpr int v = KIND == CGB_KIND_POISSON2D5 ? 256 : 128; };
+inline int box_w(int kind) { return kind == CGB_KIND_POISSON2D5 ? 256 : 128; }
 constexpr int kNC = 512;                 // consumer threads
 constexpr int kNT = kNC + 32;            // + one producer warp
 constexpr int kMaxStages = 8;
@@ -104,6 +107,7 @@ struct Taps {
 };
 
 // Offsets of a consumer thread's taps. il = x offset inside the tile, i = global x.
+template <int BW>
 __device__ __forceinline__ Taps make_taps(const BandGeo& G, int il, int i, int nx) {
   constexpr int RS = BW * 8;
   const int boxb = G.prow * RS;
@@ -131,7 +135,7 @@ __device__ __forceinline__ Taps make_taps(const BandGeo& G, int il, int i, int n
 // Plane sums for the thread's two adjacent rows from one slab. Slab row t holds band row t-1.
 template <int KIND>
 __device__ __forceinline__ void plane_from_slab(const unsigned char* slab, const Taps& tp, int ra, PS2& A, PS2& B) {
-  constexpr int RS = BW * 8;  // slab row stride in bytes
+  constexpr int RS = BoxW<KIND>::v * 8;  // slab row stride in bytes
   const unsigned char* b0 = slab + ra * RS;
   auto ld2 = [&](int row) { return *reinterpret_cast<const double2*>(b0 + row * RS + tp.c); };
   auto ldl = [&](int row) { return tp.l >= 0 ? *reinterpret_cast<const double*>(slab + tp.l + (ra + row) * tp.ls) : 0.0; };
@@ -171,7 +175,7 @@ template <int KIND>
 __device__ __forceinline__ void plane_from_two(const unsigned char* rslab, const unsigned char* pslab, const Taps& tp,
                                                int ra, double beta, bool ghost, PS2& A, PS2& B, double2& pna,
                                                double2& pnb) {
-  constexpr int RS = BW * 8;
+  constexpr int RS = BoxW<KIND>::v * 8;
   const unsigned char* r0 = rslab + ra * RS;
   const unsigned char* p0 = pslab + ra * RS;
   const double bt = ghost ? 0.0 : beta;  // p_old slab holds finite data (zeros or a previous p), so 0*p is exact
@@ -282,6 +286,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
                                                       const __grid_constant__ CUtensorMap tmr,
                                                       const __grid_constant__ BandGeo G, double* __restrict__ out,
                                                       int mode) {
+  constexpr int BW = BoxW<KIND>::v;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ double red_smem[64];
   __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
@@ -360,7 +365,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
       const int i = it.x0 + il;
       const bool active = ly < G.LY && i < L.nx;
-      const Taps tp = make_taps(G, il, i, L.nx);
+      const Taps tp = make_taps<BW>(G, il, i, L.nx);
       const int ja = it.yb * G.RB + ra;
       const int jend = active ? min(L.ny, (it.yb + 1) * G.RB) : 0;
       const bool va = ja < jend, vb = ja + 1 < jend, pair = i + 1 < L.nx;
@@ -435,6 +440,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
                                                        const __grid_constant__ BandGeo G,
                                                        const double* __restrict__ pold, double* __restrict__ pnew,
                                                        int newbuf) {
+  constexpr int BW = BoxW<KIND>::v;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ double red_smem[64];
   __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
@@ -556,7 +562,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
       const int i = it.x0 + il;
       const bool active = ly < G.LY && i < L.nx;
       const bool pair = i + 1 < L.nx;
-      const Taps tp = make_taps(G, il, i, L.nx);
+      const Taps tp = make_taps<BW>(G, il, i, L.nx);
       const int ja = it.yb * G.RB + ra;
       const int jend = active ? min(L.ny, (it.yb + 1) * G.RB) : 0;
       const bool va = ja < jend, vb = ja + 1 < jend;
@@ -639,6 +645,7 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
   G.RB = flat ? 1 : 2 * G.LY;
   G.HY = flat ? 0 : 1;
   G.prow = G.RB + 2 * G.HY;
+  const int BW = box_w(P.st.kind);
   G.NBX = (tile + BW - 1) / BW;
   G.nby = (L.ny + G.RB - 1) / G.RB;
   G.nbands = G.ntx * G.nby;
@@ -708,6 +715,7 @@ int spmv_tma_make_map(int kind, const cgb_layout_t& L, const double* vec, void* 
   if (!make_geo(P, 148, kSpmvAlpha, &G, &grid, &sm)) return fail(CGB_ERR_UNSUPPORTED, "layout not supported by the TMA SpMV");
   cuuint64_t dims[3] = {(cuuint64_t)L.nx, (cuuint64_t)L.py, (cuuint64_t)L.pz};
   cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.pitch * L.py * 8};
+  if (box_cols != 2) box_cols = box_w(kind);  // main boxes; 2 = the x-halo boxes of tiled rows
   cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)(halo_rows ? G.prow : G.RB), 1};
   cuuint32_t es[3] = {1, 1, 1};
   CUresult r = enc((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(vec), dims, strides,
