@@ -114,3 +114,39 @@ def test_gpu_multi_gpu_restart_from_x_file(cli, tmp_path):
     np.testing.assert_allclose(c, a, atol=1e-7 * np.abs(a).max())
     full, resumed = json.loads(ja.read_text()), json.loads(jc.read_text())
     assert resumed["status"] == 1 and resumed["r0norm"] < full["r0norm"]
+
+
+def test_python_module_cli_cpu_paths(tmp_path):
+    # python -m cuda_mpi_parallel_b200: reference stdout on the CPU path, and BASELINE config 1 over gloo (2 ranks)
+    import os
+    import sys
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--device", "cpu"], capture_output=True, text=True,
+                       timeout=300, env=env)
+    assert r.returncode == 0 and r.stdout == REFERENCE_STDOUT, r.stdout + r.stderr
+    h = tmp_path / "h.txt"
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29911", "-m", "cuda_mpi_parallel_b200", "--problem", "poisson2d5",
+                        "--grid", "64", "64", "--device", "cpu", "--hist-out", str(h)], capture_output=True, text=True,
+                       timeout=300, env=env)
+    assert r.returncode == 0 and "Success" in r.stdout, r.stdout + r.stderr
+    prob = Problem.poisson2d(64, 64)
+    ref = cpu_cg(prob, prob.rhs("ones"))
+    hist = np.array([float(l.split()[1]) for l in h.read_text().splitlines()])
+    assert len(hist) == ref.iters
+    np.testing.assert_allclose(hist, ref.history, rtol=1e-9)
+
+
+@pytest.mark.gpu
+def test_python_module_cli_gpu(tmp_path):
+    import os
+    import sys
+    j = tmp_path / "j.json"
+    r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout == REFERENCE_STDOUT, r.stdout + r.stderr
+    r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--problem", "poisson3d7", "--n", "48", "--graph", "while",
+                        "--json-out", str(j)], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout == "Success\n", r.stdout + r.stderr
+    meta = json.loads(j.read_text())
+    prob = Problem.poisson3d(48)
+    assert meta["status"] == 1 and abs(meta["iters"] - cpu_cg(prob, prob.rhs("ones")).iters) <= 1
