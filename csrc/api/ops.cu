@@ -167,6 +167,27 @@ extern "C" int cgb_op_unpad(const cgb_layout_t* lay, const double* padded, doubl
   return CGB_OK;
 }
 
+// Band-kernel geometry for a local box (no GPU needed): out = {LX, LY, RB, HY, slab rows, boxes per row, x tiles,
+// row bands, bands, z chunks, planes per chunk, work items, stage bytes, stages, grid, halo CTAs}. Returns 1 if the
+// TMA kernels cover the layout, 0 otherwise. mode: 0 SpMV, 4 update, 5 merged p-update+SpMV.
+extern "C" int cgb_debug_tma_geometry(const cgb_stencil_t* st, const cgb_layout_t* lay, int nbr_lo, int nbr_hi, int nsm,
+                                      int mode, int* out16) {
+  if (!st || !lay || !out16) return 0;
+  RankDev P{};
+  P.st = *st;
+  P.lay = *lay;
+  for (int d = 0; d < CGB_NDIR; ++d) P.nbr[d] = -1;
+  if (nbr_lo) {
+    P.nbr[dir_index(0, -1)] = 0;
+    P.nbr_mask |= 1u << dir_index(0, -1);
+  }
+  if (nbr_hi) {
+    P.nbr[dir_index(0, 1)] = 0;
+    P.nbr_mask |= 1u << dir_index(0, 1);
+  }
+  return spmv_tma_geometry(P, nsm, mode, out16);
+}
+
 extern "C" int cgb_device_count(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) {

@@ -38,6 +38,7 @@ cudaError_t launch_spmv_simple(const RankDev& P, const LaunchCfg& c, const doubl
                                int mode, cudaStream_t s);
 // TMA-fed stencil SpMV (spmv_tma.cu). `map` points at a 128-byte CUtensorMap of the input vector.
 bool spmv_tma_supported(const RankDev& P);
+int spmv_tma_geometry(const RankDev& P, int nsm, int mode, int out[16]);
 int spmv_tma_make_map(int kind, const cgb_layout_t& L, const double* vec, void* map_out, int halo_rows = 1,
                       int box_cols = 128);
 // map_h: the input's 2-column halo-box map (rows wider than 512 cells). map_x / map_r (halo_rows = 0 maps of

@@ -693,6 +693,18 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
 
 }  // namespace
 
+// Geometry of the band kernels for inspection/tests (host only, needs no GPU).
+int spmv_tma_geometry(const RankDev& P, int nsm, int mode, int out[16]) {
+  BandGeo G;
+  int grid;
+  size_t sm;
+  if (!make_geo(P, nsm, mode, &G, &grid, &sm)) return 0;
+  const int v[16] = {G.LX, G.LY, G.RB, G.HY, G.prow, G.NBX, G.ntx, G.nby, G.nbands, G.zs, G.zchunk, G.nitems,
+                     G.stage_bytes, G.nstages, grid, G.nhalo};
+  for (int k = 0; k < 16; ++k) out[k] = v[k];
+  return 1;
+}
+
 bool spmv_tma_supported(const RankDev& P) {
   BandGeo G;
   int grid;

@@ -122,6 +122,7 @@ def _declare(lib):
         "cgb_op_p_update": (C.c_int, [P(Layout), dbl, vp, vp, vp, vp]),
         "cgb_op_pad": (C.c_int, [P(Layout), vp, vp, vp]),
         "cgb_op_unpad": (C.c_int, [P(Layout), vp, vp, vp]),
+        "cgb_debug_tma_geometry": (C.c_int, [P(Stencil), P(Layout), C.c_int, C.c_int, C.c_int, C.c_int, P(C.c_int)]),
         "cgb_version": (C.c_char_p, []),
         "cgb_last_error": (C.c_char_p, []),
         "cgb_device_count": (C.c_int, []),

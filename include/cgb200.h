@@ -279,6 +279,10 @@ int cgb_op_p_update(const cgb_layout_t* lay, double beta, const double* r, doubl
 int cgb_op_pad(const cgb_layout_t* lay, const double* compact, double* padded, void* stream);
 int cgb_op_unpad(const cgb_layout_t* lay, const double* padded, double* compact, void* stream);
 
+/* Geometry the TMA band kernels would use for a local box (host only, for tests and tuning): see csrc/api/ops.cu. */
+int cgb_debug_tma_geometry(const cgb_stencil_t* st, const cgb_layout_t* lay, int nbr_lo, int nbr_hi, int nsm,
+                           int mode, int* out16);
+
 /* ---- misc ---- */
 const char* cgb_version(void);
 const char* cgb_last_error(void);
