@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
   }
   double a = acc, z = 0.0;
   if (grid_sum2_last(a, z, P.partials, &S.ticket_red, red_smem)) {
+    if (P.csr_dist) ready_publish(P, version);  // distributed CSR: my rows of p0 are complete
     bool ok = allreduce2_last_cta(P, a, z, red_smem);
     if (threadIdx.x == 0) {
       S.rho = a;
@@ -325,13 +326,23 @@ __global__ void __launch_bounds__(kThreads) k_spmv_csr(const __grid_constant__ R
   const int lane = threadIdx.x % G;
   const int gpb = kThreads / G;
   double acc = 0.0;
+  // Row-block distributed matrix: entries of p owned by other ranks are loaded straight from the
+  // owners' arenas over NVLink, once every rank has announced that its part of this p is complete.
+  const bool dist = P.csr_dist != 0;
+  if (dist && !ready_wait(P, S.halo_seq)) return;
+  auto fetch = [&](int c) -> double {
+    if (!dist) return in[c];
+    int li;
+    const int q = csr_owner(P.csr_n_global, P.nranks, c, li);
+    return q == P.rank ? in[li] : P.peer_exch0[q][li];
+  };
   // The trip count depends only on blockIdx, so every lane of a warp reaches the shuffles.
   for (int base = blockIdx.x * gpb; base < n; base += gridDim.x * gpb) {
     const int row = base + threadIdx.x / G;
     const bool valid = row < n;
     const int e0 = valid ? P.csr_rowptr[row] : 0, e1 = valid ? P.csr_rowptr[row + 1] : 0;
     double s = 0.0;
-    for (int e = e0 + lane; e < e1; e += G) s += P.csr_val[e] * in[P.csr_colind[e]];
+    for (int e = e0 + lane; e < e1; e += G) s += P.csr_val[e] * fetch(P.csr_colind[e]);
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o, G);
     if (valid && lane == 0) {
@@ -474,6 +485,21 @@ __global__ void __launch_bounds__(kThreads) k_pupdate(const __grid_constant__ Ra
         vp[q].y = vr[q].y + beta * vp[q].y;
         st2(p + idx[q], vp[q]);
       }
+  }
+  if (P.csr_dist) {
+    // distributed CSR has no geometric halo: the last CTA tells every rank that this rank's rows of
+    // the new p are in memory; the peers' SpMV then loads what it needs by index
+    __shared__ int s_last;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      s_last = atomicAdd(&S.ticket_red, 1u) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (s_last) {
+      if (threadIdx.x == 0) S.ticket_red = 0u;
+      ready_publish(P, version);
+    }
   }
 }
 

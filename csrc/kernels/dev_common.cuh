@@ -59,6 +59,7 @@ struct Control {
   u64 red_ll[kRedSlots][CGB_MAX_RANKS][4];
   u64 halo_flag[CGB_NDIR];  // [d]: newest version pushed into my ghost layer by neighbour nbr[d]
   u64 pad_[7];
+  u64 ready_flag[CGB_MAX_RANKS];  // distributed CSR: [q] = newest version of p that rank q has completed
   Scalars s;
 };
 static_assert(sizeof(Control) <= kCtrlBytes, "control block overflow");
@@ -88,6 +89,10 @@ struct RankDev {
   const int* csr_colind;
   const double* csr_val;
   int csr_avg_nnz;   // ceil(nnz/n): picks the lanes-per-row of k_spmv_csr
+  // row-block distributed CSR: remote entries of p are loaded from the owners' exchange buffers
+  int csr_dist;                          // 1 if the columns span several ranks
+  int csr_n_global;
+  double* peer_exch0[CGB_MAX_RANKS];     // exchange buffer 0 (p) of every rank, as mapped here
   // SpMV work decomposition (host-chosen)
   int ntx, nty, nmc, mchunk;
 };
@@ -381,6 +386,39 @@ __device__ __forceinline__ bool halo_wait_all(const RankDev& P, u64 version) {
   }
   __syncthreads();
   return s_hok != 0;
+}
+
+// ---- distributed CSR: "my part of p, version v, is complete" ----
+
+// Owner rank and local index of global row/column c under the block distribution of block_range().
+__device__ __forceinline__ int csr_owner(int n, int nranks, int c, int& local) {
+  const int base = n / nranks, rem = n % nranks, cut = rem * (base + 1);
+  int q;
+  if (c < cut) {
+    q = c / (base + 1);
+    local = c - q * (base + 1);
+  } else {
+    q = rem + (c - cut) / base;
+    local = c - cut - (q - rem) * base;
+  }
+  return q;
+}
+// All threads of the LAST CTA of a kernel that wrote p (every other CTA has passed its ticket).
+__device__ __forceinline__ void ready_publish(const RankDev& P, u64 version) {
+  __threadfence_system();
+  if ((int)threadIdx.x < P.nranks) st_release_sys(&P.peer_ctrl[threadIdx.x]->ready_flag[P.rank], version);
+}
+// All threads of a CTA that is about to read remote entries of p.
+__device__ __forceinline__ bool ready_wait(const RankDev& P, u64 version) {
+  __shared__ int s_rok;
+  if (threadIdx.x == 0) s_rok = 1;
+  __syncthreads();
+  if ((int)threadIdx.x < P.nranks && !spin_until_ge(&P.ctrl->ready_flag[threadIdx.x], version, P.ctrl->s.timeout_cycles)) {
+    s_rok = 0;
+    P.ctrl->s.done = CGB_ERR_TIMEOUT;
+  }
+  __syncthreads();
+  return s_rok != 0;
 }
 
 // ---- elementwise unit mapping: unit u -> pair of x-cells in owned row (j,k) ----

@@ -137,6 +137,7 @@ int ctx_finalize_peers(cgb_ctx* c) {
   for (int q = 0; q < c->part.nranks; ++q) {
     if (!c->peer_base[q]) return fail(CGB_ERR_STATE, "rank %d: peer %d not attached", c->part.rank, q);
     P.peer_ctrl[q] = (Control*)c->peer_base[q];
+    P.peer_exch0[q] = (double*)((char*)c->peer_base[q] + kExchOff);
   }
   const int pw = (c->lay.nx + 1) / 2;
   for (int d = 0; d < CGB_NDIR; ++d) {
@@ -218,6 +219,45 @@ extern "C" int cgb_ctx_create_csr(int32_t n, int64_t nnz, const int32_t* rowptr,
   c->P.csr_colind = c->d_colind;
   c->P.csr_val = c->d_val;
   c->P.csr_avg_nnz = (int)((nnz + n - 1) / n);
+  *out = c;
+  return CGB_OK;
+}
+
+extern "C" int cgb_ctx_create_csr_dist(int32_t n_global, const cgb_partition_t* part, int64_t nnz, const int32_t* rowptr,
+                                       const int32_t* colind, const double* val, int device, int hist_cap,
+                                       cgb_ctx** out) {
+  CGB_REQUIRE(n_global > 0 && part && nnz > 0 && rowptr && colind && val && out, "cgb_ctx_create_csr_dist: bad argument");
+  CGB_REQUIRE(nnz < INT_MAX, "int32 row offsets: nnz must be < 2^31");
+  CGB_REQUIRE(part->nx >= 1 && part->x0 >= 0 && part->x0 + part->nx <= n_global, "row block out of range");
+  const int n = part->nx;
+  cgb_ctx* c = new cgb_ctx();
+  c->device = device;
+  c->hist_cap = hist_cap;
+  int rc = cgb_stencil_default(CGB_KIND_CSR, n_global, 1, 1, &c->st);
+  c->part = *part;
+  if (rc == 0) rc = make_layout(c->st, c->part, &c->lay);
+  if (rc == 0) rc = alloc_common(c);
+  auto stage = [&]() -> int {
+    CGB_CUDA(cudaMalloc(&c->d_rowptr, (size_t)(n + 1) * sizeof(int)));
+    CGB_CUDA(cudaMalloc(&c->d_colind, (size_t)nnz * sizeof(int)));
+    CGB_CUDA(cudaMalloc(&c->d_val, (size_t)nnz * sizeof(double)));
+    CGB_CUDA(cudaMemcpy(c->d_rowptr, rowptr, (size_t)(n + 1) * sizeof(int), cudaMemcpyHostToDevice));
+    CGB_CUDA(cudaMemcpy(c->d_colind, colind, (size_t)nnz * sizeof(int), cudaMemcpyHostToDevice));
+    CGB_CUDA(cudaMemcpy(c->d_val, val, (size_t)nnz * sizeof(double), cudaMemcpyHostToDevice));
+    return CGB_OK;
+  };
+  if (rc == 0) rc = stage();
+  if (rc != 0) {
+    delete c;
+    return rc;
+  }
+  c->csr_nnz = nnz;
+  c->P.csr_rowptr = c->d_rowptr;
+  c->P.csr_colind = c->d_colind;
+  c->P.csr_val = c->d_val;
+  c->P.csr_avg_nnz = (int)((nnz + n - 1) / n);
+  c->P.csr_dist = part->nranks > 1 ? 1 : 0;
+  c->P.csr_n_global = n_global;
   *out = c;
   return CGB_OK;
 }
@@ -582,6 +622,8 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_MERGED2, "unknown variant %d", o->variant);
   if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
     return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
+  if (c->P.csr_dist && (o->variant == CGB_VAR_PIPELINED || o->warm_start))
+    return fail(CGB_ERR_UNSUPPORTED, "distributed CSR supports the fused variant from x0 = 0 only");
   if (o->variant == CGB_VAR_MERGED2 && !merged2_ok(c))
     return fail(CGB_ERR_UNSUPPORTED, "the merged variant needs the TMA SpMV (3D stencil, nx <= 512) and a z-slab decomposition");
   CGB_CUDA(cudaSetDevice(c->device));

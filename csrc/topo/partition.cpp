@@ -13,8 +13,17 @@ int make_partition(const cgb_stencil_t& st, int nranks, int rank, int decomp, in
   CGB_REQUIRE(rank >= 0 && rank < nranks, "rank %d out of range [0,%d)", rank, nranks);
   const bool is3d = kind_is_3d(st.kind);
   if (st.kind == CGB_KIND_CSR) {
-    CGB_REQUIRE(nranks == 1, "general CSR problems are single-rank (multi-GPU CSR is not implemented)");
-    Py = Pz = 1;
+    // general CSR: contiguous row blocks, no geometric neighbours (remote entries are fetched by index)
+    CGB_REQUIRE(nranks <= st.gx, "more ranks than rows");
+    cgb_partition_t p{};
+    p.nranks = nranks;
+    p.rank = rank;
+    p.Py = p.Pz = 1;
+    block_range(st.gx, nranks, rank, &p.x0, &p.nx);
+    p.ny = p.nz = 1;
+    for (int d = 0; d < CGB_NDIR; ++d) p.nbr[d] = -1;
+    *out = p;
+    return CGB_OK;
   } else if (!is3d) {
     // 2D grids are nx x 1 x ny: only the row (z) direction can be split
     CGB_REQUIRE(Py == 0 || Py == 1, "2D problems are split along their rows only");

@@ -35,7 +35,7 @@ class Stencil(C.Structure):
 class Partition(C.Structure):
     _fields_ = [("nranks", C.c_int32), ("rank", C.c_int32), ("Py", C.c_int32), ("Pz", C.c_int32),
                 ("ry", C.c_int32), ("rz", C.c_int32), ("nx", C.c_int32), ("y0", C.c_int32),
-                ("ny", C.c_int32), ("z0", C.c_int32), ("nz", C.c_int32), ("nbr", C.c_int32 * NDIR)]
+                ("ny", C.c_int32), ("z0", C.c_int32), ("nz", C.c_int32), ("nbr", C.c_int32 * NDIR), ("x0", C.c_int32)]
 
 
 class Layout(C.Structure):
@@ -91,6 +91,7 @@ def _declare(lib):
         "cgb_solve_opts_default": (None, [P(SolveOpts)]),
         "cgb_ctx_create": (C.c_int, [P(Stencil), P(Partition), C.c_int, C.c_int, P(vp)]),
         "cgb_ctx_create_csr": (C.c_int, [i32, i64, vp, vp, vp, C.c_int, C.c_int, P(vp)]),
+        "cgb_ctx_create_csr_dist": (C.c_int, [i32, P(Partition), i64, vp, vp, vp, C.c_int, C.c_int, P(vp)]),
         "cgb_ctx_destroy": (C.c_int, [vp]),
         "cgb_ctx_ipc_export": (C.c_int, [vp, vp]),
         "cgb_ctx_peer_attach_ipc": (C.c_int, [vp, C.c_int, vp]),

@@ -68,7 +68,16 @@ class CGSolver:
         self.maxit_cap = maxit_cap
         L = N.lib()
         ctx = C.c_void_p()
-        if problem.is_csr:
+        if problem.is_csr and nranks > 1:
+            # row-block distributed CSR: this rank's rows, local row offsets, global column indices
+            r0, r1 = self.part.x0, self.part.x0 + self.part.nx
+            e0, e1 = int(problem.rowptr[r0]), int(problem.rowptr[r1])
+            self._csr_local = (np.ascontiguousarray(problem.rowptr[r0:r1 + 1] - e0, dtype=np.int32),
+                               np.ascontiguousarray(problem.colind[e0:e1]), np.ascontiguousarray(problem.val[e0:e1]))
+            rp, ci, va = self._csr_local
+            N.check(L.cgb_ctx_create_csr_dist(problem.n, C.byref(self.part), e1 - e0, rp.ctypes.data, ci.ctypes.data,
+                                              va.ctypes.data, self.device, maxit_cap, C.byref(ctx)))
+        elif problem.is_csr:
             N.check(L.cgb_ctx_create_csr(problem.n, int(problem.val.size), problem.rowptr.ctypes.data,
                                          problem.colind.ctypes.data, problem.val.ctypes.data, self.device,
                                          maxit_cap, C.byref(ctx)))

@@ -31,11 +31,18 @@ def local_slices(problem, part: N.Partition):
 
 
 def scatter_global(problem, part: N.Partition, g: np.ndarray) -> np.ndarray:
+    if problem.is_csr:                       # row block of a general CSR problem
+        return np.ascontiguousarray(np.asarray(g)[part.x0:part.x0 + part.nx])
     gx, gy, gz = problem.dims
     return np.ascontiguousarray(g.reshape(gz, gy, gx)[local_slices(problem, part)]).reshape(-1)
 
 
 def gather_global(problem, parts, locals_) -> np.ndarray:
+    if problem.is_csr:
+        out = np.zeros(problem.n)
+        for part, loc in zip(parts, locals_):
+            out[part.x0:part.x0 + part.nx] = np.asarray(loc)
+        return out
     gx, gy, gz = problem.dims
     out = np.zeros((gz, gy, gx))
     for part, loc in zip(parts, locals_):

@@ -91,6 +91,7 @@ typedef struct cgb_partition_t {
   int32_t y0, ny;        /* owned y range */
   int32_t z0, nz;        /* owned z range */
   int32_t nbr[CGB_NDIR]; /* neighbour rank per direction, -1 if none/not needed by the stencil */
+  int32_t x0;            /* general CSR only: first global row of this rank's row block (nx = rows owned) */
 } cgb_partition_t;
 
 /* Py,Pz == 0 picks: decomp=1 -> z slabs (row blocks for 2D grids), decomp=2 (3D only) -> the most square
@@ -193,6 +194,13 @@ int cgb_ctx_create(const cgb_stencil_t* st, const cgb_partition_t* part, int dev
  * (CUDACG.cu:120-134). */
 int cgb_ctx_create_csr(int32_t n, int64_t nnz, const int32_t* rowptr, const int32_t* colind,
                        const double* val, int device, int hist_cap, cgb_ctx** out);
+/* Row-block distributed general CSR (goes beyond the reference, which is single-GPU): this rank owns the
+ * rows [part.x0, part.x0 + part.nx) of an n_global x n_global matrix (cgb_partition_make with a CSR
+ * descriptor); rowptr is local (0-based, nx+1 entries), colind holds GLOBAL column indices. The SpMV
+ * reads remote entries of p directly from the owners' arenas over NVLink (peer loads), after a
+ * release/acquire hand-over of "p version v is complete"; variant FUSED only. */
+int cgb_ctx_create_csr_dist(int32_t n_global, const cgb_partition_t* part, int64_t nnz_local, const int32_t* rowptr,
+                            const int32_t* colind, const double* val, int device, int hist_cap, cgb_ctx** out);
 int cgb_ctx_destroy(cgb_ctx* c);
 
 /* Fabric: every rank exports its arena, every rank attaches all peers it talks to. */

@@ -23,7 +23,12 @@ def main():
     from cuda_mpi_parallel_b200 import Problem, cpu_cg
     from cuda_mpi_parallel_b200.parallel.partition import gather_global, make_partition, scatter_global
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    prob = Problem.from_name(name, dims)
+    if name.startswith("csr-"):
+        # a general CSR problem (here: an assembled stencil operator) distributed by row blocks
+        rowptr, colind, val = Problem.from_name(name[4:], dims).to_csr()
+        prob = Problem.csr(rowptr, colind, val)
+    else:
+        prob = Problem.from_name(name, dims)
     b = prob.rhs("random", seed=21)
     part = make_partition(prob, world, rank, decomp)
     b_local = scatter_global(prob, part, b)

@@ -97,3 +97,16 @@ def test_gpu_fabric_soak_thousands_of_handshakes():
     nproc = 2 if n < 4 else 4
     res = _run(nproc, ["soak", "poisson3d7", "32x16x24", "1", "merged"], port=29780, timeout=300)
     assert res["ok"], res
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("name,dims", [("csr-stencil3d27", "13x11x9"), ("csr-poisson2d5", "70x45")])
+def test_gpu_distributed_general_csr(name, dims):
+    # beyond the reference (single GPU): row-block CSR whose SpMV loads remote entries of p over NVLink
+    n = _ngpu()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    nproc = 2 if n < 4 else 4
+    res = _run(nproc, ["gpu", name, dims, "1", "fused"], port=29790, timeout=240)
+    assert res["ok"] and res["ranks_identical"], res

@@ -60,3 +60,13 @@ def test_partition_invariance(prob, configs, variant):
         big = ref.history[:n] > 1e-6 * ref.r0norm
         np.testing.assert_allclose(s.history[:n][big], ref.history[:n][big], rtol=1e-8)
         np.testing.assert_allclose(s.x, ref.x, atol=1e-7)
+
+
+def test_csr_row_block_partition():
+    p = Problem.poisson2d(7, 5)
+    rowptr, colind, val = p.to_csr()
+    pc = Problem.csr(rowptr, colind, val)
+    parts = [make_partition(pc, 4, r) for r in range(4)]
+    assert [q.x0 for q in parts] == [0, 9, 18, 27] and [q.nx for q in parts] == [9, 9, 9, 8]
+    g = np.arange(pc.n, dtype=float)
+    np.testing.assert_array_equal(gather_global(pc, parts, [scatter_global(pc, q, g) for q in parts]), g)
