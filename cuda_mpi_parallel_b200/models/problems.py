@@ -78,6 +78,22 @@ class Problem:
         return cls(name, cls._stencil(N.KIND_CSR, n, 1, 1), rowptr, colind, val)
 
     @classmethod
+    def from_scipy(cls, A, name: str = "csr") -> "Problem":
+        """General CSR problem from any scipy sparse matrix (converted to CSR with sorted int32 indices)."""
+        import scipy.sparse as sp
+        A = sp.csr_matrix(A, dtype=np.float64)
+        if A.shape[0] != A.shape[1]:
+            raise ValueError("matrix must be square")
+        A.sort_indices()
+        return cls.csr(A.indptr, A.indices, A.data, name=name)
+
+    @classmethod
+    def from_matrix_market(cls, path, name: str = "csr") -> "Problem":
+        """General CSR problem from a MatrixMarket file (symmetric files are expanded), like `cgb200 --problem csr:F`."""
+        import scipy.io
+        return cls.from_scipy(scipy.io.mmread(str(path)), name=name)
+
+    @classmethod
     def ref3x3(cls) -> "Problem":
         """The reference's system: A=[[3,0,2],[0,2,0],[2,0,1]], b=(3.5,1.5,2), x=(0.5,0.75,1)."""
         n, nnz = C.c_int32(), C.c_int32()

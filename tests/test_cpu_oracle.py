@@ -75,3 +75,18 @@ def test_pipelined_variant_converges_to_same_solution():
     p = cpu_cg(prob, b, tol=1e-9, variant="pipelined")
     assert p.converged and abs(p.iters - c.iters) <= max(2, c.iters // 10)
     np.testing.assert_allclose(p.x, c.x, atol=1e-7)
+
+
+def test_problem_from_scipy_and_matrix_market(tmp_path):
+    import scipy.io
+    import scipy.sparse as sp
+    A = sp.random(40, 40, density=0.1, random_state=3)
+    A = (A + A.T + 40 * sp.identity(40)).tocoo()          # SPD by diagonal dominance
+    p1 = Problem.from_scipy(A)
+    scipy.io.mmwrite(str(tmp_path / "a.mtx"), A)
+    p2 = Problem.from_matrix_market(tmp_path / "a.mtx")
+    assert (p1.to_scipy() != p2.to_scipy()).nnz == 0
+    b = np.arange(1.0, 41.0)
+    s = cpu_cg(p1, b, tol=1e-10)
+    assert s.converged
+    np.testing.assert_allclose(p1.to_scipy() @ s.x, b, atol=1e-8)
