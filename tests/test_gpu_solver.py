@@ -269,3 +269,19 @@ def test_2d_problems_on_the_tma_kernels(prob, variant):
     big = ref.history[:n] > 1e-5 * ref.r0norm
     np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-5 if variant == "pipelined" else 1e-8)
     np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6 * max(1.0, np.abs(ref.x).max()))
+
+
+def test_iterate_streamed_copies_each_residual_to_pinned_memory():
+    import torch
+    prob = Problem.poisson3d(40, 36, 44)
+    s = CGSolver(prob)
+    s.set_rhs("random", seed=43)
+    hist = torch.zeros(12, dtype=torch.float64).pin_memory()
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        s.begin(fixed_iters=12, stream=st)
+        s.iterate_streamed(12, hist)
+        st.synchronize()
+        res = s.finish()
+    assert res.iters == 12
+    np.testing.assert_array_equal(hist.numpy(), s.history(12))
