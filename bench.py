@@ -21,9 +21,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
-import statistics
 import sys
-import threading
 import time
 from pathlib import Path
 
@@ -31,51 +29,7 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 
-class ClockSampler:
-    """Samples SM clock and throttle reasons of one GPU through NVML while the timed region runs."""
-
-    def __init__(self, index: int, period_s: float = 0.005):
-        self.index, self.period = index, period_s
-        self.samples, self.reasons = [], set()
-        self.max_mhz = None
-        self._stop = threading.Event()
-        self._t = None
-
-    def _run(self):
-        try:
-            import pynvml as nv
-            nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.index)
-            self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-            names = {
-                nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
-                nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
-                nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
-                nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
-                nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
-            }
-            while not self._stop.is_set():
-                self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
-                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for bit, name in names.items():
-                    if r & bit:
-                        self.reasons.add(name)
-                time.sleep(self.period)
-        except Exception as e:  # NVML missing: report that instead of inventing clocks
-            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
-
-    def __enter__(self):
-        self._t = threading.Thread(target=self._run, daemon=True)
-        self._t.start()
-        return self
-
-    def __exit__(self, *a):
-        self._stop.set()
-        self._t.join(timeout=2)
-
-    def summary(self):
-        return {"sm_mhz": statistics.median(self.samples) if self.samples else None,
-                "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+from cuda_mpi_parallel_b200.utils.clocks import ClockSampler  # noqa: E402  (NVML sampling during the timed region)
 
 
 def parse():
@@ -90,7 +44,12 @@ def parse():
     ap.add_argument("--spmv", default=os.environ.get("CGB_SPMV", "auto"))
     ap.add_argument("--decomp", type=int, default=1)
     ap.add_argument("--chunk", type=int, default=0)
+    ap.add_argument("--persistent", default="auto", choices=["auto", "on", "off"],
+                    help="merged variant: one persistent cooperative kernel per chunk (auto/on) or two kernels per iteration (off)")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--trace", action="store_true",
+                    help="persistent kernel: record device timestamps at both barriers of every iteration and add a "
+                         "per-iteration time budget (compute vs rendezvous, per rank) to the JSON line")
     return ap.parse_args()
 
 
@@ -139,15 +98,21 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    persistent = {"auto": None, "on": True, "off": False}[a.persistent]
+    clk = ClockSampler(local_rank).start()      # NVML is up before any timed window opens
+
     # ---- kernel-only arm: device-resident RHS, K iterations between CUDA events ------------------
+    trace = torch.zeros(4 * (W + K), dtype=torch.int64, device="cuda") if a.trace else None
+    if trace is not None:
+        solver.set_trace(trace)
     with torch.cuda.stream(stream):
         solver.set_rhs("random", seed=1)
-        solver.begin(fixed_iters=W + K, variant=a.variant, spmv=a.spmv, chunk=chunk, stream=stream)
+        solver.begin(fixed_iters=W + K, variant=a.variant, spmv=a.spmv, chunk=chunk, stream=stream, persistent=persistent)
         solver.iterate(W)
         barrier()
         l0 = solver.launch_count
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with ClockSampler(local_rank) as clk:
+        with clk:
             e0.record(stream)
             solver.iterate(K)
             e1.record(stream)
@@ -160,12 +125,30 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
+    budget = None
+    if trace is not None:
+        solver.set_trace(None)
+        ts = trace.cpu().numpy().reshape(-1, 4)[W:W + K].astype("float64") * 1e-3     # us, timed iterations only
+        if (ts > 0).all() and K > 2:
+            import numpy as np
+            mine = {"rank": rank,
+                    "phaseA_us": float(np.median(ts[1:, 0] - ts[:-1, 3])), "rendezvousA_us": float(np.median(ts[:, 1] - ts[:, 0])),
+                    "phaseB_us": float(np.median(ts[:, 2] - ts[:, 1])), "rendezvousB_us": float(np.median(ts[:, 3] - ts[:, 2])),
+                    "iteration_us": float(np.median(ts[1:, 3] - ts[:-1, 3]))}
+        else:
+            mine = {"rank": rank, "note": "no persistent-kernel timestamps (variant without the persistent kernel?)"}
+        budget = [mine]
+        if world > 1:
+            budget = [None] * world
+            dist.all_gather_object(budget, mine)
 
     # ---- end-to-end arm: public API, RHS from pinned host memory, residual read back every step ---
     e2e = None
     if not a.no_e2e:
+        # the same hash-random RHS as the kernel arm, generated from the GLOBAL index: the residuals below do not
+        # depend on how many ranks share the grid
         b_host = torch.empty(solver.n_local, dtype=torch.float64).pin_memory()
-        b_host.uniform_(-1.0, 1.0)
+        prob.rhs_local(solver.part, "random", seed=1, out=b_host)
         hist = torch.zeros(K, dtype=torch.float64).pin_memory()
         solver.set_host_history(hist)          # every step's ||r||_2 lands in pinned host memory (8-byte D2H per step)
         with torch.cuda.stream(stream):
@@ -174,14 +157,14 @@ def main():
                 barrier()
                 t0 = time.perf_counter()
                 solver.set_rhs(b_host, stream=stream)                       # H2D of this solve's input
-                solver.begin(fixed_iters=K, variant=a.variant, spmv=a.spmv, chunk=chunk, stream=stream)
+                solver.begin(fixed_iters=K, variant=a.variant, spmv=a.spmv, chunk=chunk, stream=stream, persistent=persistent)
                 solver.iterate(K + (1 if a.variant == "pipelined" else 0))   # pipelined CG learns ||r_K|| one update later
                 stream.synchronize()
                 rn_last = float(hist[K - 1])                                # host reads the results
                 assert rn_last > 0.0 and float(hist[0]) > 0.0, "residuals did not reach host memory"
                 barrier()
                 t1 = time.perf_counter()
-                solver.finish()
+                e2e_r0 = solver.finish().r0norm
         solver.set_host_history(None)
         te = torch.tensor([t1 - t0], dtype=torch.float64, device="cuda")
         if world > 1:
@@ -190,7 +173,8 @@ def main():
                "h2d_bytes_per_step": solver.n_local * 8 / K, "d2h_bytes_per_step": 8,
                "note": "CG has no per-iteration input: the rank's RHS slab is copied H2D from pinned memory once "
                        "inside the timed region (bytes amortised over the K steps); every step's ||r||_2 is "
-                       "stored device->host (zero-copy into pinned memory) and read by the host", "last_rnorm": rn_last}
+                       "stored device->host (zero-copy into pinned memory) and read by the host",
+               "r0norm": e2e_r0, "last_rnorm": rn_last}
 
     if rank == 0:
         n = prob.n
@@ -205,11 +189,19 @@ def main():
             "config": {"model": f"{a.problem} {'x'.join(map(str, grid))} fp64 unpreconditioned CG",
                        "global_batch": n, "seq_len": None,
                        "parallelism": f"{'z-slab' if a.decomp == 1 else '2d'} domain decomposition x{world}",
-                       "variant": a.variant, "spmv": a.spmv, "graph_chunk": chunk,
-                       "l2": "inputs larger than L2 (no flush): %.0f MB per vector per rank" %
-                             (solver.layout.vec_elems * 8 / 1e6)},
+                       "variant": a.variant, "spmv": a.spmv, "graph_chunk": chunk, "persistent": a.persistent,
+                       "l2": "inputs larger than L2 (no flush): an iteration streams 4 vectors of %.0f MB per rank "
+                             "(8 vector passes, %.0f MB) through the 126 MB L2" %
+                             (solver.layout.vec_elems * 8 / 1e6, 8 * solver.layout.vec_elems * 8 / 1e6)},
+            # deterministic kernel arm: ||r|| after W+K iterations from the hash-random RHS; must not depend on N
+            "r0norm": res.r0norm, "rnorm_after_steps": res.rnorm, "iters_run": res.iters,
             "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches), "impl": "ours",
         }
+        if budget is not None:
+            # phase = from the release of the previous barrier to the arrival of this rank's last CTA (compute + skew
+            # inside the rank); rendezvous = from that arrival to the release (partial sum, all-reduce over NVLink,
+            # i.e. waiting for the slowest rank, scalar update)
+            out["iteration_budget_us"] = budget
         print(json.dumps(out))
     if world > 1:
         dist.barrier()

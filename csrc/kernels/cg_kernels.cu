@@ -14,48 +14,6 @@ namespace cgb {
 
 namespace {
 
-__device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
-__device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<double2*>(p) = v; }
-
-// ---------------------------------------------------------------------------------------------
-// boundary-row enumeration for the "boundary first" pass of the p producers
-// ---------------------------------------------------------------------------------------------
-struct BRows {
-  int nA, nB, nC, nD, klo, total;
-};
-__device__ __forceinline__ BRows brows_make(const cgb_layout_t& L) {
-  BRows B;
-  B.nA = L.gz ? L.ny : 0;                  // plane k = 0
-  B.nB = (L.gz && L.nz > 1) ? L.ny : 0;    // plane k = nz-1
-  B.klo = L.gz ? 1 : 0;
-  int khi = L.gz ? L.nz - 1 : L.nz;
-  B.nC = L.gy ? max(0, khi - B.klo) : 0;   // rows j = 0 of the remaining planes
-  B.nD = (L.gy && L.ny > 1) ? B.nC : 0;    // rows j = ny-1
-  B.total = B.nA + B.nB + B.nC + B.nD;
-  return B;
-}
-__device__ __forceinline__ void brow_to_jk(const BRows& B, const cgb_layout_t& L, int b, int& j, int& k) {
-  if (b < B.nA) { j = b; k = 0; return; }
-  b -= B.nA;
-  if (b < B.nB) { j = b; k = L.nz - 1; return; }
-  b -= B.nB;
-  if (b < B.nC) { j = 0; k = B.klo + b; return; }
-  b -= B.nC;
-  j = L.ny - 1;
-  k = B.klo + b;
-}
-
-// Store a pair into every neighbour ghost layer the row belongs to; count units per direction.
-__device__ __forceinline__ void push_pair(const RankDev& P, int exch_buf, unsigned mask, int i, int j, int k,
-                                          double2 v, unsigned* cnt) {
-  while (mask) {
-    int d = __ffs(mask) - 1;
-    mask &= mask - 1;
-    st2(P.nbr_exch[exch_buf][d] + ghost_index(P, d, i, j, k), v);
-    atomicAdd(&cnt[d], 1u);
-  }
-}
-
 // ---------------------------------------------------------------------------------------------
 // k_init: r = b, p = b, x = 0 (the reference never initialises x on the device, CUDACG.cu:182-186),
 // rho = b.b (CUDACG.cu:261-266 without the sqrt/square round trip), halo push of p0.
@@ -205,14 +163,14 @@ struct PS {
 };
 
 template <int KIND>
-__device__ __forceinline__ void plane_center(const double* __restrict__ in, int64_t idx, PS& o) {
+__device__ __forceinline__ void plane_center(const double* in, int64_t idx, PS& o) {
   double2 c = ld2(in + idx);
   o.s0[0] = c.x;
   o.s0[1] = c.y;
 }
 
 template <int KIND>
-__device__ __forceinline__ void plane_full(const double* __restrict__ in, int64_t idx, int i, int nx, int pitch,
+__device__ __forceinline__ void plane_full(const double* in, int64_t idx, int i, int nx, int pitch,
                                            PS& o) {
   const bool has_l = i > 0, has_r = i + 2 < nx;
   const double2 c = ld2(in + idx);
@@ -238,8 +196,11 @@ __device__ __forceinline__ void plane_full(const double* __restrict__ in, int64_
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kThreads) k_spmv(const __grid_constant__ RankDev P, const double* __restrict__ in,
-                                                    double* __restrict__ out, int mode) {
+// `in` is deliberately NOT __restrict__: its ghost layers are written by peer GPUs while this kernel runs, so
+// the loads must stay ordinary (coherent) global loads ordered by the acquire in halo_wait_all; with __restrict__
+// the compiler turns them into ld.global.nc (LDG.CONSTANT), which the memory model does not order after an acquire.
+__global__ void __launch_bounds__(kThreads) k_spmv(const __grid_constant__ RankDev P, const double* in, double* out,
+                                                    int mode) {
   __shared__ double red_smem[64];
   Scalars& S = P.ctrl->s;
   if (S.done != 0) return;

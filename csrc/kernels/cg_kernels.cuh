@@ -48,6 +48,12 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
 // "merged" variant: p-update folded into the SpMV (maps: r with halo rows, p_old, p_new buffers).
 cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const maps[6], const double* pold, double* pnew,
                              int newbuf, cudaStream_t s);
+// Persistent cooperative kernel: `niter` whole iterations of the merged variant in one launch (grid barrier +
+// all-reduce on the device). maps: r with halo rows, exch[0], exch[1], their three halo-box twins, x, r (band rows).
+cudaError_t launch_cg_persist(const RankDev& P, int device, const void* const maps[8], int cur, int niter,
+                              cudaStream_t s);
+bool cg_persist_supported(int device);
+cudaError_t cg_persist_prepare(int device);  // one-time per-device set-up (allocates): call from the prepare path
 cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* in, double* out, int mode,
                             cudaStream_t s);
 // x += alpha p; r -= alpha Ap; rho' = all-reduce(r.r); convergence test; beta.

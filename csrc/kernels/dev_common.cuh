@@ -40,6 +40,7 @@ struct Scalars {
   u64 pub_seq;       // pipelined CG: sequence number of the reduction published by the last update
   u64 red_seq;       // sequence number of the next all-reduce this rank will publish
   u64 halo_seq;      // version of the newest halo this rank has pushed / expects
+  u64 gbar;          // persistent kernel: generation of the last completed grid barrier (never reset by a solve)
   long long timeout_cycles;
   int tol_mode;
   int iter;          // completed iterations
@@ -83,6 +84,10 @@ struct RankDev {
   int hist_cap;
   double* hist_host;  // optional mapped pinned host buffer: ||r|| of every iteration is also stored there
   int hist_host_cap;
+  // optional device buffer (persistent kernel): per iteration 4 x %globaltimer ns - last CTA reached barrier A,
+  // alpha released, last CTA reached barrier B, beta released. Gives the compute / rendezvous split of an iteration.
+  unsigned long long* trace;
+  int trace_cap;      // iterations the buffer can hold
   double2* partials;
   // CSR problems
   const int* csr_rowptr;
@@ -454,6 +459,46 @@ __device__ __forceinline__ int64_t ghost_index(const RankDev& P, int d, int i, i
   const int jn = dy < 0 ? P.nbr_ny[d] : (dy > 0 ? -1 : j);
   const int kn = dz < 0 ? P.nbr_nz[d] : (dz > 0 ? -1 : k);
   return (int64_t)i + (int64_t)P.lay.pitch * ((int64_t)(jn + P.lay.gy) + (int64_t)P.nbr_py[d] * (int64_t)(kn + P.lay.gz));
+}
+
+// ---- boundary-row enumeration for the "boundary first" pass of the kernels that write the SpMV input ----
+__device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
+__device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<double2*>(p) = v; }
+
+struct BRows {
+  int nA, nB, nC, nD, klo, total;
+};
+__device__ __forceinline__ BRows brows_make(const cgb_layout_t& L) {
+  BRows B;
+  B.nA = L.gz ? L.ny : 0;                  // plane k = 0
+  B.nB = (L.gz && L.nz > 1) ? L.ny : 0;    // plane k = nz-1
+  B.klo = L.gz ? 1 : 0;
+  int khi = L.gz ? L.nz - 1 : L.nz;
+  B.nC = L.gy ? max(0, khi - B.klo) : 0;   // rows j = 0 of the remaining planes
+  B.nD = (L.gy && L.ny > 1) ? B.nC : 0;    // rows j = ny-1
+  B.total = B.nA + B.nB + B.nC + B.nD;
+  return B;
+}
+__device__ __forceinline__ void brow_to_jk(const BRows& B, const cgb_layout_t& L, int b, int& j, int& k) {
+  if (b < B.nA) { j = b; k = 0; return; }
+  b -= B.nA;
+  if (b < B.nB) { j = b; k = L.nz - 1; return; }
+  b -= B.nB;
+  if (b < B.nC) { j = 0; k = B.klo + b; return; }
+  b -= B.nC;
+  j = L.ny - 1;
+  k = B.klo + b;
+}
+
+// Store a pair into every neighbour ghost layer the row belongs to; count units per direction.
+__device__ __forceinline__ void push_pair(const RankDev& P, int exch_buf, unsigned mask, int i, int j, int k,
+                                          double2 v, unsigned* cnt) {
+  while (mask) {
+    int d = __ffs(mask) - 1;
+    mask &= mask - 1;
+    st2(P.nbr_exch[exch_buf][d] + ghost_index(P, d, i, j, k), v);
+    atomicAdd(&cnt[d], 1u);
+  }
 }
 
 }  // namespace cgb

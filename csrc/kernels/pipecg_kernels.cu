@@ -17,43 +17,6 @@ namespace cgb {
 
 namespace {
 
-__device__ __forceinline__ double2 ld2(const double* p) { return *reinterpret_cast<const double2*>(p); }
-__device__ __forceinline__ void st2(double* p, double2 v) { *reinterpret_cast<double2*>(p) = v; }
-
-struct BRowsP {
-  int nA, nB, nC, nD, klo, total;
-};
-__device__ __forceinline__ BRowsP brows_make_p(const cgb_layout_t& L) {
-  BRowsP B;
-  B.nA = L.gz ? L.ny : 0;
-  B.nB = (L.gz && L.nz > 1) ? L.ny : 0;
-  B.klo = L.gz ? 1 : 0;
-  int khi = L.gz ? L.nz - 1 : L.nz;
-  B.nC = L.gy ? max(0, khi - B.klo) : 0;
-  B.nD = (L.gy && L.ny > 1) ? B.nC : 0;
-  B.total = B.nA + B.nB + B.nC + B.nD;
-  return B;
-}
-__device__ __forceinline__ void brow_to_jk_p(const BRowsP& B, const cgb_layout_t& L, int b, int& j, int& k) {
-  if (b < B.nA) { j = b; k = 0; return; }
-  b -= B.nA;
-  if (b < B.nB) { j = b; k = L.nz - 1; return; }
-  b -= B.nB;
-  if (b < B.nC) { j = 0; k = B.klo + b; return; }
-  b -= B.nC;
-  j = L.ny - 1;
-  k = B.klo + b;
-}
-__device__ __forceinline__ void push_pair_p(const RankDev& P, int exch_buf, unsigned mask, int i, int j, int k,
-                                            double2 v, unsigned* cnt) {
-  while (mask) {
-    int d = __ffs(mask) - 1;
-    mask &= mask - 1;
-    st2(P.nbr_exch[exch_buf][d] + ghost_index(P, d, i, j, k), v);
-    atomicAdd(&cnt[d], 1u);
-  }
-}
-
 // Runs `body(idx, push_mask, i, j, k)` over all owned pairs: boundary rows first (then the halo
 // flags are raised), interior afterwards.
 template <class Body>
@@ -65,12 +28,12 @@ __device__ __forceinline__ void for_pairs_boundary_first(const RankDev& P, unsig
   if (P.nbr_mask) {
     if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
     __syncthreads();
-    const BRowsP B = brows_make_p(L);
+    const BRows B = brows_make(L);
     const unsigned UA = (unsigned)B.total * (unsigned)um.pw;
     for (unsigned u = tid0; u < UA; u += stride) {
       unsigned brow = u / (unsigned)um.pw;
       int i = 2 * (int)(u - brow * (unsigned)um.pw), j, k;
-      brow_to_jk_p(B, L, (int)brow, j, k);
+      brow_to_jk(B, L, (int)brow, j, k);
       unsigned mask = row_push_mask(L, j, k) & P.nbr_mask;
       if (!mask) continue;
       body(lay_index(L, i, j, k), mask, i, j, k);
@@ -104,7 +67,7 @@ __global__ void __launch_bounds__(kThreads) k_pipe_start(const __grid_constant__
     st2(P.pp + idx, zero2);
     g += vr.x * vr.x + vr.y * vr.y;
     d += vw.x * vr.x + vw.y * vr.y;
-    if (mask) push_pair_p(P, wbuf, mask, i, j, k, vw, cnt);
+    if (mask) push_pair(P, wbuf, mask, i, j, k, vw, cnt);
   });
   if (grid_sum2_last(g, d, P.partials, &S.ticket_red, red_smem)) {
     allreduce2_publish(P, g, d, red_smem);
@@ -161,7 +124,7 @@ __global__ void __launch_bounds__(kThreads) k_pipe_update(const __grid_constant_
       st2(wn + idx, vn);
       g += vr.x * vr.x + vr.y * vr.y;
       d += vn.x * vr.x + vn.y * vr.y;
-      if (mask) push_pair_p(P, wbuf ^ 1, mask, i, j, k, vn, cnt);
+      if (mask) push_pair(P, wbuf ^ 1, mask, i, j, k, vn, cnt);
     });
   }
   if (grid_sum2_last(g, d, P.partials, &S.ticket_red, red_smem)) {

@@ -221,25 +221,62 @@ __device__ __forceinline__ void plane_from_two(const unsigned char* rslab, const
   }
 }
 
-// OUT: 0 store Ap and accumulate p.Ap; 1 accumulate p.Ap only; 2 x += alpha p, r -= alpha Ap,
-// accumulate r.r (x/r pairs were prefetched one plane ahead into vx/vr).
-template <int KIND, int OUT>
-__device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out, const PS2& pv, const PS2& cu,
-                                     const PS2& nx, int64_t idx, bool pair, double alpha, double2 vx, double2 vr,
-                                     double& acc) {
+// Partial-sum formulation of the z sweep. With the in-plane sums S0 (centre), S1 (4 faces), S2 (4 diagonals)
+// of plane k, define
+//   C_k = cc*S0_k + cf*S1_k + ce*S2_k     plane k's own contribution to output plane k
+//   T_k = cf*S0_k + ce*S1_k + cn*S2_k     plane k's contribution to output planes k-1 and k+1
+// so that Ap_k = C_k + T_{k-1} + T_{k+1}. A thread therefore carries three values per cell along the sweep -
+// part = C_k + T_{k-1}, T_k and S0_k - instead of the six (S0,S1,S2 of two planes) of the direct form; for the
+// 5/7-point stencils T_k = cf*S0_k is not even stored. This is what keeps the 27-point kernels and the
+// persistent kernel inside the 96 registers a 544-thread CTA can have, without spills in the inner loops.
+struct Run2 {
+  double part[2], t[2], s0[2];
+};
+
+template <int KIND>
+__device__ __forceinline__ void plane_ct(const RankDev& P, const PS2& n, double c[2], double t[2]) {
   const double cc = P.st.c_center, cf = P.st.c_face;
-  double a0 = cc * cu.s0[0] + cf * (cu.s1[0] + (pv.s0[0] + nx.s0[0]));
-  double a1 = cc * cu.s0[1] + cf * (cu.s1[1] + (pv.s0[1] + nx.s0[1]));
-  if (KIND == CGB_KIND_STENCIL3D27) {
-    const double ce = P.st.c_edge, cn = P.st.c_corner;
-    a0 += ce * (cu.s2[0] + (pv.s1[0] + nx.s1[0])) + cn * (pv.s2[0] + nx.s2[0]);
-    a1 += ce * (cu.s2[1] + (pv.s1[1] + nx.s1[1])) + cn * (pv.s2[1] + nx.s2[1]);
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    if (KIND == CGB_KIND_STENCIL3D27) {
+      const double ce = P.st.c_edge, cn = P.st.c_corner;
+      c[e] = cc * n.s0[e] + (cf * n.s1[e] + ce * n.s2[e]);
+      t[e] = cf * n.s0[e] + (ce * n.s1[e] + cn * n.s2[e]);
+    } else {
+      c[e] = cc * n.s0[e] + cf * n.s1[e];
+      t[e] = cf * n.s0[e];
+    }
   }
+}
+
+// The newly arrived plane becomes the current one.
+template <int KIND>
+__device__ __forceinline__ void run_advance(const RankDev& P, Run2& A, const PS2& n, const double c[2], const double t[2]) {
+#pragma unroll
+  for (int e = 0; e < 2; ++e) {
+    if (KIND == CGB_KIND_STENCIL3D27) {
+      A.part[e] = c[e] + A.t[e];
+      A.t[e] = t[e];
+    } else {
+      A.part[e] = c[e] + P.st.c_face * A.s0[e];
+    }
+    A.s0[e] = n.s0[e];
+  }
+}
+
+// Output of the current plane once its upper neighbour's T has arrived.
+// OUT: 0 store Ap and accumulate p.Ap; 1 accumulate p.Ap only; 2 x += alpha p, r -= alpha Ap,
+// accumulate r.r (the x/r pairs of the emitted plane arrive TMA-staged in vx/vr).
+template <int KIND, int OUT>
+__device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out, const Run2& A, const double tn[2],
+                                     int64_t idx, bool pair, double alpha, double2 vx, double2 vr, double& acc) {
+  const double a0 = A.part[0] + tn[0];
+  const double a1 = A.part[1] + tn[1];
   if (OUT == 2) {
-    vx.x += alpha * cu.s0[0];
+    vx.x += alpha * A.s0[0];
     vr.x -= alpha * a0;
     if (pair) {
-      vx.y += alpha * cu.s0[1];
+      vx.y += alpha * A.s0[1];
       vr.y -= alpha * a1;
       *reinterpret_cast<double2*>(P.x + idx) = vx;
       *reinterpret_cast<double2*>(P.r + idx) = vr;
@@ -255,7 +292,7 @@ __device__ __forceinline__ void emit(const RankDev& P, double* __restrict__ out,
     if (pair) *reinterpret_cast<double2*>(out + idx) = make_double2(a0, a1);
     else out[idx] = a0;
   }
-  acc += cu.s0[0] * a0 + (pair ? cu.s0[1] * a1 : 0.0);
+  acc += A.s0[0] * a0 + (pair ? A.s0[1] * a1 : 0.0);
 }
 
 struct Item {
@@ -278,52 +315,63 @@ __device__ __forceinline__ Item make_item(const RankDev& P, const BandGeo& G, in
   return it;
 }
 
-template <int KIND, int OUT>
-__global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ RankDev P,
-                                                      const __grid_constant__ CUtensorMap tmap,
-                                                      const __grid_constant__ CUtensorMap tmap_h,
-                                                      const __grid_constant__ CUtensorMap tmx,
-                                                      const __grid_constant__ CUtensorMap tmr,
-                                                      const __grid_constant__ BandGeo G, double* __restrict__ out,
-                                                      int mode) {
-  constexpr int BW = BoxW<KIND>::v;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ double red_smem[64];
-  __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
-  Scalars& S = P.ctrl->s;
-  if (S.done != 0) return;
-  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
-  const unsigned kStages = (unsigned)G.nstages;
+// State of one mbarrier ring: smem addresses of the full/empty barrier arrays and the number of slabs this
+// thread's role has issued (producer lane) or consumed (consumer threads) so far. A persistent kernel keeps
+// one Ring per phase alive across iterations; the per-iteration kernels start one at zero.
+struct Ring {
+  unsigned full0, empty0;
+  unsigned n;
+};
+
+__device__ __forceinline__ void ring_init(Ring& R, unsigned long long* bars, int nstages) {
+  R.full0 = smem_u32(bars);
+  R.empty0 = smem_u32(bars + kMaxStages);
+  R.n = 0;
   if (threadIdx.x == 0) {
-    for (unsigned s = 0; s < kStages; ++s) {
-      mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, kNC / 32);
+    for (int s = 0; s < nstages; ++s) {
+      mbar_init(R.full0 + 8 * s, 1);
+      mbar_init(R.empty0 + 8 * s, kNC / 32);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
+}
 
+// One sweep of the band SpMV over this CTA's items (all threads of the CTA call it; warp kNC/32 is the TMA
+// producer, the others consume). acc receives this thread's share of p.Ap (OUT 0/1) or r.r (OUT 2).
+// halo_version: the halo version the ghost layers of the input must have reached before they are loaded.
+template <int KIND, int OUT>
+__device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, const CUtensorMap* tmap,
+                                           const CUtensorMap* tmap_h, const CUtensorMap* tmx, const CUtensorMap* tmr,
+                                           double* __restrict__ out, double alpha, u64 halo_version,
+                                           unsigned char* smem_raw, Ring& R, double& acc) {
+  constexpr int BW = BoxW<KIND>::v;
+  Scalars& S = P.ctrl->s;
+  // Opaque copies of the thread/block index: in the persistent kernel this keeps everything derived from them
+  // (tap offsets, row indices) local to the phase instead of hoisted out of the iteration loop and held in
+  // registers (or spilled) across the other phase.
+  unsigned tid = threadIdx.x, bid = blockIdx.x;
+  asm volatile("" : "+r"(tid), "+r"(bid));
+  const unsigned full0 = R.full0, empty0 = R.empty0;
+  const unsigned kStages = (unsigned)G.nstages;
   const cgb_layout_t& L = P.lay;
   const bool nb_zlo = P.nbr[dir_index(0, -1)] >= 0, nb_zhi = P.nbr[dir_index(0, 1)] >= 0;
   const bool nb_ylo = P.nbr[dir_index(-1, 0)] >= 0, nb_yhi = P.nbr[dir_index(1, 0)] >= 0;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const double alpha = S.alpha;
-  double acc = 0.0;
+  const int warp = tid >> 5, lane = tid & 31;
+  unsigned n = R.n;
 
   if (warp == kNC / 32) {
     // ===== producer warp: one lane issues every TMA load =====
     if (lane == 0) {
-      unsigned n = 0;
       bool waited = false;
       auto wait_flags = [&]() {
         if (waited) return;
         for (int d = 0; d < CGB_NDIR; ++d)
-          if (d != 4 && P.nbr[d] >= 0 && !spin_until_ge(&P.ctrl->halo_flag[d], S.halo_seq, S.timeout_cycles))
+          if (d != 4 && P.nbr[d] >= 0 && !spin_until_ge(&P.ctrl->halo_flag[d], halo_version, S.timeout_cycles))
             S.done = CGB_ERR_TIMEOUT;
         asm volatile("fence.proxy.async;" ::: "memory");
         waited = true;
       };
-      for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
+      for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
         if (it.y_ghost) wait_flags();
         const int y0 = it.yb * G.RB;  // padded row of band row -1
@@ -338,16 +386,16 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
           mbar_expect_tx(full0 + 8 * st, p_tx + (with_xr ? 2u * (unsigned)G.xr_bytes : 0u));
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
           for (int b = 0; b < G.NBX; ++b)
-            tma_load_3d(dst + b * G.prow * BW * 8, &tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + b * G.prow * BW * 8, tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
           if (G.ntx > 1) {  // the tile's x halo: two 2-column boxes (zero-filled outside the domain)
-            tma_load_3d(dst + G.h_off, &tmap_h, it.x0 - 2, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.h_off + 128, &tmap_h, it.x0 + 2 * G.LX, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.h_off, tmap_h, it.x0 - 2, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.h_off + 128, tmap_h, it.x0 + 2 * G.LX, y0, q + 1, full0 + 8 * st);
           }
           if (with_xr) {
             const int ko = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
             for (int b = 0; b < G.NBX; ++b) {
-              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, &tmx, it.x0 + b * BW, y0 + G.HY, ko + 1, full0 + 8 * st);
-              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, &tmr, it.x0 + b * BW, y0 + G.HY, ko + 1,
+              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, tmx, it.x0 + b * BW, y0 + G.HY, ko + 1, full0 + 8 * st);
+              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, tmr, it.x0 + b * BW, y0 + G.HY, ko + 1,
                           full0 + 8 * st);
             }
           }
@@ -356,12 +404,11 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
     }
   } else {
     // ===== consumer warps =====
-    const int lx = threadIdx.x % G.LX, ly = threadIdx.x / G.LX;
+    const int lx = tid % G.LX, ly = tid / G.LX;
     const int il = 2 * lx;
     const int ra = 2 * ly;
     const int xr_off = (il / BW) * (G.RB * BW * 8) + (ra * BW + il % BW) * 8;
-    unsigned n = 0;
-    for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
+    for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
       const int i = it.x0 + il;
       const bool active = ly < G.LY && i < L.nx;
@@ -373,12 +420,16 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;           // signed plane stride along the sweep
       // index of (i, ja) on the plane emitted at step 2, then advanced by ps per step
       int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);
-      PS2 pa, pb, ca, cb, na, nb;
+      Run2 A{}, B{};
       for (int s = 0; s < nsteps; ++s, ++n) {
         const unsigned st = n % kStages, ph = (n / kStages) & 1u;
         mbar_wait(full0 + 8 * st, ph);
         const unsigned char* stage = smem_raw + (size_t)st * G.stage_bytes;
+        PS2 na{}, nb{};
         if (active) plane_from_slab<KIND>(stage, tp, ra, na, nb);
+        double ca[2], ta[2], cb[2], tb[2];
+        plane_ct<KIND>(P, na, ca, ta);
+        plane_ct<KIND>(P, nb, cb, tb);
         double2 cxa = make_double2(0, 0), cxb = cxa, cra = cxa, crb = cxa;
         if (OUT == 2 && s >= 2 && active) {  // x and r rows of the plane emitted now (TMA-staged)
           const unsigned char* xs = stage + G.p_bytes + xr_off;
@@ -392,15 +443,36 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
         if (s >= 2) {
-          if (va) emit<KIND, OUT>(P, out, pa, ca, na, idx, pair, alpha, cxa, cra, acc);
-          if (vb) emit<KIND, OUT>(P, out, pb, cb, nb, idx + L.pitch, pair, alpha, cxb, crb, acc);
+          if (va) emit<KIND, OUT>(P, out, A, ta, idx, pair, alpha, cxa, cra, acc);
+          if (vb) emit<KIND, OUT>(P, out, B, tb, idx + L.pitch, pair, alpha, cxb, crb, acc);
           idx += ps;
         }
-        pa = ca; pb = cb;
-        ca = na; cb = nb;
+        run_advance<KIND>(P, A, na, ca, ta);
+        run_advance<KIND>(P, B, nb, cb, tb);
       }
     }
   }
+  R.n = n;
+}
+
+template <int KIND, int OUT>
+__global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ RankDev P,
+                                                      const __grid_constant__ CUtensorMap tmap,
+                                                      const __grid_constant__ CUtensorMap tmap_h,
+                                                      const __grid_constant__ CUtensorMap tmx,
+                                                      const __grid_constant__ CUtensorMap tmr,
+                                                      const __grid_constant__ BandGeo G, double* __restrict__ out,
+                                                      int mode) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ double red_smem[64];
+  __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
+  Scalars& S = P.ctrl->s;
+  if (S.done != 0) return;
+  Ring R;
+  ring_init(R, bars, G.nstages);
+  __syncthreads();
+  double acc = 0.0;
+  phase_spmv<KIND, OUT>(P, G, &tmap, &tmap_h, &tmx, &tmr, out, S.alpha, S.halo_seq, smem_raw, R, acc);
   if (mode == kSpmvPlain) return;
   double a = acc, z = 0.0;
   if (grid_sum2_last_t<kNT>(a, z, P.partials, &S.ticket_red, red_smem)) {
@@ -429,39 +501,22 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
 // Replaces cublasDscal + cublasDaxpy + cusparseSpMV + cublasDdot (CUDACG.cu:342-347, 288-304).
 // z-slab decompositions only (no y neighbours).
 // ---------------------------------------------------------------------------------------------
+// All threads of the CTA. cnt: CGB_NDIR zeroed counters in shared memory (a __syncthreads() after zeroing them
+// must precede the call). acc receives this thread's share of p_new . A p_new.
 template <int KIND>
-__global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ RankDev P,
-                                                       const __grid_constant__ CUtensorMap tm_r,
-                                                       const __grid_constant__ CUtensorMap tm_pold,
-                                                       const __grid_constant__ CUtensorMap tm_pnew,
-                                                       const __grid_constant__ CUtensorMap tm_r_h,
-                                                       const __grid_constant__ CUtensorMap tm_pold_h,
-                                                       const __grid_constant__ CUtensorMap tm_pnew_h,
-                                                       const __grid_constant__ BandGeo G,
-                                                       const double* __restrict__ pold, double* __restrict__ pnew,
-                                                       int newbuf) {
+__device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, const CUtensorMap* tm_r,
+                                            const CUtensorMap* tm_pold, const CUtensorMap* tm_pnew,
+                                            const CUtensorMap* tm_r_h, const CUtensorMap* tm_pold_h,
+                                            const CUtensorMap* tm_pnew_h, const double* pold, double* pnew, int newbuf,
+                                            double beta, u64 version, unsigned* cnt, unsigned char* smem_raw, Ring& R,
+                                            double& acc) {
   constexpr int BW = BoxW<KIND>::v;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ double red_smem[64];
-  __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
-  __shared__ unsigned cnt[CGB_NDIR];
   Scalars& S = P.ctrl->s;
-  if (S.done != 0) return;
-  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
+  unsigned tid = threadIdx.x, bid = blockIdx.x;  // opaque copies, see phase_spmv
+  asm volatile("" : "+r"(tid), "+r"(bid));
+  const unsigned full0 = R.full0, empty0 = R.empty0;
   const unsigned kStages = (unsigned)G.nstages;
-  if (threadIdx.x == 0) {
-    for (unsigned s = 0; s < kStages; ++s) {
-      mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, kNC / 32);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-  __syncthreads();
-
   const cgb_layout_t& L = P.lay;
-  const double beta = S.beta;
-  const u64 version = S.halo_seq;
   const bool nb_zlo = P.nbr[dir_index(0, -1)] >= 0, nb_zhi = P.nbr[dir_index(0, 1)] >= 0;
 
   // ---- boundary planes first: push p_new of my first/last plane into the neighbours' ghosts ----
@@ -469,11 +524,12 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     const unsigned pw = (unsigned)((L.nx + 1) / 2);
     const unsigned per_plane = (unsigned)L.ny * pw;
     const unsigned total = ((nb_zlo ? 1u : 0u) + (nb_zhi ? 1u : 0u)) * per_plane;
-    // With spare SMs, dedicated CTAs (blockIdx >= nitems) push the halo while the band CTAs are
+    // With spare SMs, dedicated CTAs (blockIdx >= nctas) push the halo while the band CTAs are
     // already sweeping; otherwise every CTA takes a share before it starts.
     const bool dedicated = G.nhalo > 0;
-    const unsigned first = dedicated ? (blockIdx.x >= (unsigned)G.nctas ? (blockIdx.x - G.nctas) * kNT + threadIdx.x : total)
-                                     : blockIdx.x * kNT + threadIdx.x;
+    const bool pusher = bid >= (unsigned)G.nctas && bid < (unsigned)(G.nctas + G.nhalo);
+    const unsigned first = dedicated ? (pusher ? (bid - G.nctas) * kNT + tid : total)
+                                     : bid * kNT + tid;
     const unsigned step = (dedicated ? (unsigned)G.nhalo : gridDim.x) * kNT;
     for (unsigned u0 = first; u0 < total; u0 += 4 * step) {  // 4 units in flight per thread
       int64_t src[4], dst[4];
@@ -493,11 +549,12 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
           dst[t] = ghost_index(P, dd[t], i, j, k);
         }
       }
+      // L2 loads: in a persistent kernel these cells were rewritten by other SMs one phase ago
 #pragma unroll
       for (int t = 0; t < 4; ++t)
         if (src[t] >= 0) {
-          vr[t] = *reinterpret_cast<const double2*>(P.r + src[t]);
-          vp[t] = *reinterpret_cast<const double2*>(pold + src[t]);
+          vr[t] = __ldcg(reinterpret_cast<const double2*>(P.r + src[t]));
+          vp[t] = __ldcg(reinterpret_cast<const double2*>(pold + src[t]));
         }
 #pragma unroll
       for (int t = 0; t < 4; ++t)
@@ -511,15 +568,14 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
     halo_commit(P, cnt, version);
   }
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = tid >> 5, lane = tid & 31;
   const int boxb = G.prow * BW * 8;
-  double acc = 0.0;
+  unsigned n = R.n;
 
   if (warp == kNC / 32) {
     if (lane == 0) {
-      unsigned n = 0;
       bool waited = false;
-      for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
+      for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
         const int y0 = it.yb * G.RB;
         const int nsteps = it.k1 - it.k0 + 2;
@@ -539,25 +595,24 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
           mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
           for (int b = 0; b < G.NBX; ++b) {
-            tma_load_3d(dst + b * boxb, ghost ? &tm_pnew : &tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + b * boxb, &tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + b * boxb, ghost ? tm_pnew : tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + b * boxb, tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
           }
           if (G.ntx > 1) {
             const int xl = it.x0 - 2, xr = it.x0 + 2 * G.LX;
-            tma_load_3d(dst + G.h_off, ghost ? &tm_pnew_h : &tm_r_h, xl, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.h_off + 128, ghost ? &tm_pnew_h : &tm_r_h, xr, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + G.h_off, &tm_pold_h, xl, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + G.h_off + 128, &tm_pold_h, xr, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.h_off, ghost ? tm_pnew_h : tm_r_h, xl, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.h_off + 128, ghost ? tm_pnew_h : tm_r_h, xr, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + G.h_off, tm_pold_h, xl, y0, q + 1, full0 + 8 * st);
+            tma_load_3d(dst + G.p_bytes + G.h_off + 128, tm_pold_h, xr, y0, q + 1, full0 + 8 * st);
           }
         }
       }
     }
   } else {
-    const int lx = threadIdx.x % G.LX, ly = threadIdx.x / G.LX;
+    const int lx = tid % G.LX, ly = tid / G.LX;
     const int il = 2 * lx;
     const int ra = 2 * ly;
-    unsigned n = 0;
-    for (int item = blockIdx.x < (unsigned)G.nctas ? (int)blockIdx.x : G.nitems; item < G.nitems; item += G.nctas) {
+    for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
       const int i = it.x0 + il;
       const bool active = ly < G.LY && i < L.nx;
@@ -570,7 +625,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;
       int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);   // plane emitted at step 2
       int64_t gq = lay_index(L, i, ja, it.dir > 0 ? it.k0 - 1 : it.k1);    // plane loaded at step 0
-      PS2 pa, pb, ca, cb, na, nb;
+      Run2 A{}, B{};
       for (int s = 0; s < nsteps; ++s, ++n) {
         const unsigned st = n % kStages, ph = (n / kStages) & 1u;
         const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
@@ -579,7 +634,11 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
         mbar_wait(full0 + 8 * st, ph);
         const unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
         double2 pna = make_double2(0, 0), pnb = pna;
+        PS2 na{}, nb{};
         if (active) plane_from_two<KIND>(rs, rs + G.p_bytes, tp, ra, beta, ghost, na, nb, pna, pnb);
+        double ca[2], ta[2], cb[2], tb[2];
+        plane_ct<KIND>(P, na, ca, ta);
+        plane_ct<KIND>(P, nb, cb, tb);
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
         if (inb) {  // my two rows of p_new on the plane just loaded
@@ -595,15 +654,42 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
         gq += ps;
         if (s >= 2) {
           const double2 z2 = make_double2(0, 0);
-          if (va) emit<KIND, 1>(P, nullptr, pa, ca, na, idx, pair, 0.0, z2, z2, acc);
-          if (vb) emit<KIND, 1>(P, nullptr, pb, cb, nb, idx + L.pitch, pair, 0.0, z2, z2, acc);
+          if (va) emit<KIND, 1>(P, nullptr, A, ta, idx, pair, 0.0, z2, z2, acc);
+          if (vb) emit<KIND, 1>(P, nullptr, B, tb, idx + L.pitch, pair, 0.0, z2, z2, acc);
           idx += ps;
         }
-        pa = ca; pb = cb;
-        ca = na; cb = nb;
+        run_advance<KIND>(P, A, na, ca, ta);
+        run_advance<KIND>(P, B, nb, cb, tb);
       }
     }
   }
+  R.n = n;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ RankDev P,
+                                                       const __grid_constant__ CUtensorMap tm_r,
+                                                       const __grid_constant__ CUtensorMap tm_pold,
+                                                       const __grid_constant__ CUtensorMap tm_pnew,
+                                                       const __grid_constant__ CUtensorMap tm_r_h,
+                                                       const __grid_constant__ CUtensorMap tm_pold_h,
+                                                       const __grid_constant__ CUtensorMap tm_pnew_h,
+                                                       const __grid_constant__ BandGeo G,
+                                                       const double* __restrict__ pold, double* __restrict__ pnew,
+                                                       int newbuf) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ double red_smem[64];
+  __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
+  __shared__ unsigned cnt[CGB_NDIR];
+  Scalars& S = P.ctrl->s;
+  if (S.done != 0) return;
+  Ring R;
+  ring_init(R, bars, G.nstages);
+  if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
+  __syncthreads();
+  double acc = 0.0;
+  phase_pspmv<KIND>(P, G, &tm_r, &tm_pold, &tm_pnew, &tm_r_h, &tm_pold_h, &tm_pnew_h, pold, pnew, newbuf, S.beta,
+                    S.halo_seq, cnt, smem_raw, R, acc);
   double a = acc, z = 0.0;
   if (grid_sum2_last_t<kNT>(a, z, P.partials, &S.ticket_red, red_smem)) {
     allreduce2_last_cta(P, a, z, red_smem);
@@ -611,6 +697,176 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
       S.pAp = a;
       S.alpha = S.rho / a;
     }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// k_cg_persist: the whole "merged" CG iteration - and as many iterations as the host asks for - in ONE
+// cooperative launch, one CTA per SM. Per iteration:
+//   phase A = phase_pspmv  (p = r + beta p, boundary planes pushed to the peers first, SpMV, p.Ap)
+//   barrier  = grid-wide rendezvous fused with the cross-GPU all-reduce: the CTA that arrives last adds the
+//              per-CTA partials in index order, exchanges the rank's sum with all peers through 8-byte
+//              flag-in-data P2P stores, forms alpha and releases the other CTAs through one flag in L2
+//   phase B = phase_spmv<2> (stencil again from p, x += alpha p, r -= alpha Ap, r.r)
+//   barrier  = same, then the reference's stopping test and beta (cg_after_rr)
+// Compared with two kernels per iteration this removes two grid drains, two launches and two kernel
+// prologues from the critical path of every iteration (the per-iteration fixed cost that capped strong
+// scaling, profiles/ROOFLINE.md), and it takes the host out of the loop completely: the reference blocks
+// the host twice per iteration (CUDACG.cu:304, CUDACG.cu:328).
+// Data written through the generic proxy in one phase (p_new, x, r) is read by TMA (async proxy) in the
+// next: every thread fences (fence.proxy.async) before it arrives at the barrier and the TMA lane fences
+// again after the acquire.
+// ---------------------------------------------------------------------------------------------
+struct PersistMaps {
+  CUtensorMap rh, e[2], rh_h, e_h[2], x, r;
+};
+
+__device__ __forceinline__ u64 ld_acquire_gpu(const u64* p) {
+  u64 v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(u64* p, u64 v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Loop state of the persistent kernel lives in shared memory (accessed volatile), not in registers: the two
+// phases run at the register limit of a 544-thread CTA (96) and anything carried across them would be
+// spilled inside their inner loops.
+struct PersistState {
+  u64 seq;          // grid-barrier generation (thread 0)
+  unsigned nA, nB;  // slabs issued/consumed so far on the two mbarrier rings
+  int it;           // iterations completed by this launch
+  int stop;         // set when the solve is finished (or failed): every thread leaves the loop
+};
+
+// Everything the persistent kernel needs, in __constant__ memory (one instance per device; launch_cg_persist
+// refreshes it in stream order before every launch). The phases are out-of-line functions - inlined into the
+// iteration loop they lose ~45 registers to loop-invariant code motion and spill inside their inner loops
+// (measured with ptxas -v) - and an out-of-line function can only keep its operands in the constant bank,
+// like the per-iteration kernels do with their __grid_constant__ parameters, if they live in a __constant__
+// variable rather than in the kernel's parameter block.
+struct PersistConst {
+  RankDev P;
+  PersistMaps M;
+  BandGeo GA, GB;
+};
+__constant__ PersistConst c_pc;
+
+// phase 0: the sum is p.Ap -> alpha. phase 1: the sum is r.r -> stopping test, beta, halo version.
+__device__ __noinline__ void persist_barrier(double a, volatile PersistState* ps, double* red_smem, int phase) {
+  const RankDev& P = c_pc.P;
+  Scalars& S = P.ctrl->s;
+  double z = 0.0;
+  asm volatile("fence.proxy.async;" ::: "memory");
+  if (grid_sum2_last_t<kNT>(a, z, P.partials, &S.ticket_red, red_smem)) {
+    unsigned long long t_arrive = 0;
+    const int tslot = S.iter;  // iteration this barrier belongs to (cg_after_rr advances it)
+    if (P.trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_arrive));
+    const bool ok = allreduce2_last_cta(P, a, z, red_smem);
+    if (threadIdx.x == 0) {
+      if (phase == 0) {
+        S.pAp = a;
+        S.alpha = S.rho / a;
+      } else if (ok) {
+        cg_after_rr(P, a);
+      }
+      const u64 seq = ps->seq + 1;
+      ps->seq = seq;
+      __threadfence();
+      st_release_gpu(&S.gbar, seq);
+      if (P.trace && tslot < P.trace_cap) {
+        unsigned long long t_rel;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_rel));
+        P.trace[4 * tslot + 2 * phase] = t_arrive;
+        P.trace[4 * tslot + 2 * phase + 1] = t_rel;
+      }
+    }
+  } else if (threadIdx.x == 0) {
+    const u64 seq = ps->seq + 1;
+    ps->seq = seq;
+    const long long t0 = clock64();
+    while (ld_acquire_gpu(&S.gbar) < seq) {
+      if (clock64() - t0 > 4 * S.timeout_cycles) {  // the last CTA's own waits are bounded by timeout_cycles
+        S.done = CGB_ERR_TIMEOUT;
+        break;
+      }
+    }
+  }
+  if (threadIdx.x == 0) {
+    if (phase == 1) ps->it = ps->it + 1;
+    if (__ldcg(&S.done) != 0) ps->stop = 1;
+  }
+  __syncthreads();
+}
+
+// Phase A with the SpMV input (p_old) in exchange buffer CUR; CUR is a template parameter so that the vector
+// and tensor-map addresses stay constant-bank operands.
+template <int KIND, int CUR>
+__device__ __noinline__ double persist_phase_a(volatile PersistState* ps, unsigned long long* bars, unsigned* cnt,
+                                               unsigned char* smem_raw) {
+  constexpr int NB = CUR ^ 1;
+  const RankDev& P = c_pc.P;
+  const PersistMaps& M = c_pc.M;
+  Scalars& S = P.ctrl->s;
+  if (threadIdx.x == kNC) asm volatile("fence.proxy.async;" ::: "memory");  // TMA lane, after the barrier's acquire
+  Ring R{smem_u32(bars), smem_u32(bars + kMaxStages), ps->nA};
+  double acc = 0.0;
+  phase_pspmv<KIND>(P, c_pc.GA, &M.rh, &M.e[CUR], &M.e[NB], &M.rh_h, &M.e_h[CUR], &M.e_h[NB], P.exch[CUR], P.exch[NB], NB,
+                    __ldcg(&S.beta), __ldcg(&S.halo_seq), cnt, smem_raw, R, acc);
+  if (threadIdx.x == 0) ps->nA = R.n;
+  return acc;
+}
+
+// Phase B with the (new) SpMV input in exchange buffer NB.
+template <int KIND, int NB>
+__device__ __noinline__ double persist_phase_b(volatile PersistState* ps, unsigned long long* bars,
+                                               unsigned char* smem_raw) {
+  const RankDev& P = c_pc.P;
+  const PersistMaps& M = c_pc.M;
+  Scalars& S = P.ctrl->s;
+  if (threadIdx.x == kNC) asm volatile("fence.proxy.async;" ::: "memory");
+  Ring R{smem_u32(bars + 2 * kMaxStages), smem_u32(bars + 3 * kMaxStages), ps->nB};
+  double acc = 0.0;
+  phase_spmv<KIND, 2>(P, c_pc.GB, &M.e[NB], &M.e_h[NB], &M.x, &M.r, nullptr, __ldcg(&S.alpha), __ldcg(&S.halo_seq), smem_raw,
+                      R, acc);
+  if (threadIdx.x == 0) ps->nB = R.n;
+  return acc;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(kNT, 1) k_cg_persist(int cur0, int niter) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ double red_smem[64];
+  __shared__ __align__(8) unsigned long long bars[4 * kMaxStages];
+  __shared__ unsigned cnt[CGB_NDIR];
+  __shared__ PersistState ps_mem;
+  volatile PersistState* ps = &ps_mem;
+  Scalars& S = c_pc.P.ctrl->s;
+  Ring RA, RB;
+  ring_init(RA, bars, c_pc.GA.nstages);
+  ring_init(RB, bars + 2 * kMaxStages, c_pc.GB.nstages);
+  if (threadIdx.x == 0) {
+    // Every CTA reads the barrier generation before it can possibly move: it only advances once ALL CTAs of
+    // this launch have arrived at the first barrier.
+    ps->seq = __ldcg(&S.gbar);
+    ps->nA = 0u;
+    ps->nB = 0u;
+    ps->it = 0;
+    ps->stop = __ldcg(&S.done) != 0 ? 1 : 0;
+  }
+  __syncthreads();
+  int cur = cur0;
+#pragma unroll 1
+  while (!ps->stop && ps->it < niter) {
+    if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
+    __syncthreads();
+    double acc = cur == 0 ? persist_phase_a<KIND, 0>(ps, bars, cnt, smem_raw) : persist_phase_a<KIND, 1>(ps, bars, cnt, smem_raw);
+    persist_barrier(acc, ps, red_smem, 0);
+    if (ps->stop) break;
+    acc = cur == 0 ? persist_phase_b<KIND, 1>(ps, bars, smem_raw) : persist_phase_b<KIND, 0>(ps, bars, smem_raw);
+    persist_barrier(acc, ps, red_smem, 1);
+    cur ^= 1;
   }
 }
 
@@ -814,6 +1070,92 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const map
   else
     return cudaErrorInvalidValue;
   return cudaGetLastError();
+}
+
+namespace {
+constexpr int kSlots = 8;
+struct PersistDevice {
+  bool ready = false;
+  cudaEvent_t last_use = nullptr;       // completion of the newest launch that reads c_pc on this device
+  PersistConst* stage = nullptr;        // pinned ring: source of the asynchronous constant refresh
+  cudaEvent_t copied[kSlots] = {};      // the refresh that read slot i has executed
+  unsigned next = 0;
+};
+std::mutex g_persist_mu;
+PersistDevice g_persist_dev[64];
+}  // namespace
+
+// Per-device one-time set-up of the persistent kernel (function attributes, events, pinned staging ring).
+// It allocates, so it belongs to cgb_solve_prepare, not to the launch path. The caller has made `device` current.
+cudaError_t cg_persist_prepare(int device) {
+  if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_persist_mu);
+  PersistDevice& D = g_persist_dev[device];
+  if (D.ready) return cudaSuccess;
+  const auto at = cudaFuncAttributeMaxDynamicSharedMemorySize;
+  cudaError_t e = cudaFuncSetAttribute(k_cg_persist<CGB_KIND_POISSON3D7>, at, 220 * 1024);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_cg_persist<CGB_KIND_STENCIL3D27>, at, 220 * 1024);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_cg_persist<CGB_KIND_POISSON2D5>, at, 220 * 1024);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D.last_use, cudaEventDisableTiming);
+  for (int k = 0; k < kSlots && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&D.copied[k], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaMallocHost(&D.stage, kSlots * sizeof(PersistConst));
+  if (e != cudaSuccess) return e;
+  D.ready = true;
+  return cudaSuccess;
+}
+
+// maps: r (with halo rows), exch[0], exch[1], their three 2-column halo-box twins, then x and r (band rows).
+// The caller has made `device` current and has called cg_persist_prepare(device).
+cudaError_t launch_cg_persist(const RankDev& P, int device, const void* const maps[8], int cur, int niter,
+                              cudaStream_t s) {
+  if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(g_persist_mu);
+  PersistDevice& D = g_persist_dev[device];
+  if (!D.ready) return cudaErrorNotReady;
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device);
+  const unsigned slot = D.next++ % kSlots;
+  cudaError_t e = cudaEventSynchronize(D.copied[slot]);  // returns at once unless 8 refreshes are still queued
+  if (e != cudaSuccess) return e;
+  PersistConst& pc = D.stage[slot];
+  int ga, gb;
+  size_t sa, sb;
+  if (!make_geo(P, nsm, kSpmvPUpdate, &pc.GA, &ga, &sa) || !make_geo(P, nsm, kSpmvUpdate, &pc.GB, &gb, &sb))
+    return cudaErrorInvalidConfiguration;
+  for (int k = 0; k < 8; ++k)
+    if (!maps[k]) return cudaErrorInvalidValue;
+  pc.P = P;
+  pc.M.rh = *reinterpret_cast<const CUtensorMap*>(maps[0]);
+  pc.M.e[0] = *reinterpret_cast<const CUtensorMap*>(maps[1]);
+  pc.M.e[1] = *reinterpret_cast<const CUtensorMap*>(maps[2]);
+  pc.M.rh_h = *reinterpret_cast<const CUtensorMap*>(maps[3]);
+  pc.M.e_h[0] = *reinterpret_cast<const CUtensorMap*>(maps[4]);
+  pc.M.e_h[1] = *reinterpret_cast<const CUtensorMap*>(maps[5]);
+  pc.M.x = *reinterpret_cast<const CUtensorMap*>(maps[6]);
+  pc.M.r = *reinterpret_cast<const CUtensorMap*>(maps[7]);
+  const int grid = ga > gb ? ga : gb;    // one CTA per SM (make_geo caps both at the SM count): all co-resident
+  const size_t sm = sa > sb ? sa : sb;
+  const void* fn = P.st.kind == CGB_KIND_POISSON3D7    ? (const void*)k_cg_persist<CGB_KIND_POISSON3D7>
+                   : P.st.kind == CGB_KIND_STENCIL3D27 ? (const void*)k_cg_persist<CGB_KIND_STENCIL3D27>
+                   : P.st.kind == CGB_KIND_POISSON2D5  ? (const void*)k_cg_persist<CGB_KIND_POISSON2D5>
+                                                       : nullptr;
+  if (!fn) return cudaErrorInvalidValue;
+  // c_pc is shared by every context on this device: the refresh waits (on the device, not on the host) for the
+  // previous launch that read it, whichever stream or context that was on.
+  e = cudaStreamWaitEvent(s, D.last_use, 0);
+  if (e == cudaSuccess) e = cudaMemcpyToSymbolAsync(c_pc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaEventRecord(D.copied[slot], s);
+  if (e != cudaSuccess) return e;
+  void* args[] = {&cur, &niter};
+  // cooperative: the launch fails instead of dead-locking if the CTAs cannot all be resident at once
+  e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kNT), args, sm, s);
+  if (e == cudaSuccess) e = cudaEventRecord(D.last_use, s);
+  return e;
+}
+
+bool cg_persist_supported(int device) {
+  int coop = 0;
+  return cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, device) == cudaSuccess && coop != 0;
 }
 
 }  // namespace cgb

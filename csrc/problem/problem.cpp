@@ -114,6 +114,19 @@ extern "C" double cgb_rhs_value(const cgb_stencil_t* st, int rhs_kind, uint64_t 
   return rhs_value_ijk(*st, rhs_kind, seed, i, j, k);
 }
 
+// Owned box [y0,y0+ny) x [z0,z0+nz) (full rows) of the generated right-hand side, compact with x fastest:
+// the host-side twin of the device generator, so a rank can stage exactly the RHS the device would generate.
+extern "C" int cgb_rhs_fill_box(const cgb_stencil_t* st, int rhs_kind, uint64_t seed, int y0, int ny, int z0, int nz,
+                                double* out) {
+  if (!st || !out || ny < 0 || nz < 0 || y0 < 0 || z0 < 0 || y0 + ny > st->gy || z0 + nz > st->gz) return CGB_ERR_INVALID;
+  if (rhs_kind < CGB_RHS_ONES || rhs_kind > CGB_RHS_MANUFACTURED) return CGB_ERR_INVALID;
+  int64_t o = 0;
+  for (int k = z0; k < z0 + nz; ++k)
+    for (int j = y0; j < y0 + ny; ++j)
+      for (int i = 0; i < st->gx; ++i) out[o++] = rhs_value_ijk(*st, rhs_kind, seed, i, j, k);
+  return CGB_OK;
+}
+
 extern "C" double cgb_manufactured_u(const cgb_stencil_t* st, int64_t gidx) {
   int i = (int)(gidx % st->gx);
   int j = (int)((gidx / st->gx) % st->gy);

@@ -52,7 +52,8 @@ int alloc_common(cgb_ctx* c) {
   CGB_CUDA(cudaEventCreate(&c->ev_end));
   CGB_CUDA(cudaEventCreateWithFlags(&c->ev_poll[0], cudaEventDisableTiming));
   CGB_CUDA(cudaEventCreateWithFlags(&c->ev_poll[1], cudaEventDisableTiming));
-  CGB_CUDA(cudaMallocHost(&c->h_scal, 2 * sizeof(Scalars)));
+  CGB_CUDA(cudaEventCreateWithFlags(&c->ev_poll_nb, cudaEventDisableTiming));
+  CGB_CUDA(cudaMallocHost(&c->h_scal, 3 * sizeof(Scalars)));
 
   RankDev& P = c->P;
   P = RankDev{};
@@ -117,6 +118,7 @@ cgb_ctx::~cgb_ctx() {
   if (ev_end) cudaEventDestroy(ev_end);
   if (ev_poll[0]) cudaEventDestroy(ev_poll[0]);
   if (ev_poll[1]) cudaEventDestroy(ev_poll[1]);
+  if (ev_poll_nb) cudaEventDestroy(ev_poll_nb);
   if (own_stream) cudaStreamDestroy(own_stream);
 }
 
@@ -189,10 +191,25 @@ extern "C" int cgb_ctx_create(const cgb_stencil_t* st, const cgb_partition_t* pa
   return CGB_OK;
 }
 
+// Host-side sanity of a CSR triple before it reaches the device: a bad offset or column index would make the
+// SpMV read out of bounds (over peer mappings in the distributed case).
+static int validate_csr(int64_t nrows, int64_t ncols, int64_t nnz, const int32_t* rowptr, const int32_t* colind) {
+  CGB_REQUIRE(rowptr[0] == 0, "CSR: rowptr[0] must be 0 (got %d)", rowptr[0]);
+  for (int64_t r = 0; r < nrows; ++r)
+    CGB_REQUIRE(rowptr[r + 1] >= rowptr[r], "CSR: rowptr is not monotone at row %lld", (long long)r);
+  CGB_REQUIRE((int64_t)rowptr[nrows] == nnz, "CSR: rowptr[n] = %d does not match nnz = %lld", rowptr[nrows], (long long)nnz);
+  for (int64_t e = 0; e < nnz; ++e)
+    CGB_REQUIRE(colind[e] >= 0 && (int64_t)colind[e] < ncols, "CSR: column index %d at entry %lld is outside [0,%lld)",
+                colind[e], (long long)e, (long long)ncols);
+  return CGB_OK;
+}
+
 extern "C" int cgb_ctx_create_csr(int32_t n, int64_t nnz, const int32_t* rowptr, const int32_t* colind,
                                   const double* val, int device, int hist_cap, cgb_ctx** out) {
   CGB_REQUIRE(n > 0 && nnz > 0 && rowptr && colind && val && out, "cgb_ctx_create_csr: bad argument");
   CGB_REQUIRE(nnz < INT_MAX, "int32 row offsets: nnz must be < 2^31");
+  CGB_REQUIRE(hist_cap >= 1, "hist_cap must be >= 1");
+  CGB_TRY(validate_csr(n, n, nnz, rowptr, colind));
   cgb_ctx* c = new cgb_ctx();
   c->device = device;
   c->hist_cap = hist_cap;
@@ -230,6 +247,8 @@ extern "C" int cgb_ctx_create_csr_dist(int32_t n_global, const cgb_partition_t* 
   CGB_REQUIRE(nnz < INT_MAX, "int32 row offsets: nnz must be < 2^31");
   CGB_REQUIRE(part->nx >= 1 && part->x0 >= 0 && part->x0 + part->nx <= n_global, "row block out of range");
   const int n = part->nx;
+  CGB_REQUIRE(hist_cap >= 1, "hist_cap must be >= 1");
+  CGB_TRY(validate_csr(n, n_global, nnz, rowptr, colind));
   cgb_ctx* c = new cgb_ctx();
   c->device = device;
   c->hist_cap = hist_cap;
@@ -444,6 +463,15 @@ extern "C" int cgb_ctx_set_host_history(cgb_ctx* c, double* pinned, int cap) {
   return CGB_OK;
 }
 
+extern "C" int cgb_ctx_set_trace(cgb_ctx* c, unsigned long long* dev_buf, int cap_iters) {
+  CGB_REQUIRE(c, "cgb_ctx_set_trace: NULL context");
+  CGB_REQUIRE(!dev_buf || cap_iters > 0, "cgb_ctx_set_trace: cap must be positive");
+  c->P.trace = dev_buf;
+  c->P.trace_cap = dev_buf ? cap_iters : 0;
+  cgb::ctx_drop_graphs(c);  // captured kernels hold a copy of P
+  return CGB_OK;
+}
+
 extern "C" int64_t cgb_ctx_launch_count(cgb_ctx* c) { return c ? c->launches : 0; }
 
 // ---------------------------------------------------------------------------------------------
@@ -459,6 +487,7 @@ extern "C" void cgb_solve_opts_default(cgb_solve_opts_t* o) {
   o->spmv_impl = CGB_SPMV_AUTO;
   o->use_graph = 1;
   o->chunk = 25;
+  o->persistent = 0;
 }
 
 namespace cgb {
@@ -495,8 +524,17 @@ static int enqueue_spmv(cgb_ctx* c, int buf, int mode, cudaStream_t s) {
   return CGB_OK;
 }
 
+// `n` iterations of the merged variant in ONE cooperative launch (grid barrier + all-reduce on the device).
+static int enqueue_persist(cgb_ctx* c, int n, cudaStream_t s) {
+  const void* maps[8] = {c->tmap_rh, c->tmap[0], c->tmap[1], c->tmap_rh_h, c->tmap_h[0], c->tmap_h[1], c->tmap_x, c->tmap_r};
+  CGB_CUDA(launch_cg_persist(c->P, c->device, maps, c->host_cur, n, s));
+  c->host_cur ^= (n & 1);
+  return CGB_OK;
+}
+
 int ctx_enqueue_iteration(cgb_ctx* c, cudaStream_t s) {
   const RankDev& P = c->P;
+  if (c->use_persist) return enqueue_persist(c, 1, s);
   if (c->opts.variant == CGB_VAR_PIPELINED) {
     CGB_TRY(enqueue_spmv(c, c->host_cur, kSpmvPlain, s));            // q = A w
     CGB_CUDA(launch_pipe_update(P, c->cfg, c->host_cur, s));         // consumes (gamma,delta), publishes the next
@@ -621,11 +659,11 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   NvtxRange nvtx_("cgb.solve_prepare");
   CGB_REQUIRE(o->variant >= CGB_VAR_FUSED && o->variant <= CGB_VAR_MERGED2, "unknown variant %d", o->variant);
   if (o->variant == CGB_VAR_MERGED && !c->tma_ok)
-    return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA SpMV (3D stencil, nx <= 512)");
+    return fail(CGB_ERR_UNSUPPORTED, "the recompute variant needs the TMA band kernels (stencil problems only)");
   if (c->P.csr_dist && (o->variant == CGB_VAR_PIPELINED || o->warm_start))
     return fail(CGB_ERR_UNSUPPORTED, "distributed CSR supports the fused variant from x0 = 0 only");
   if (o->variant == CGB_VAR_MERGED2 && !merged2_ok(c))
-    return fail(CGB_ERR_UNSUPPORTED, "the merged variant needs the TMA SpMV (3D stencil, nx <= 512) and a z-slab decomposition");
+    return fail(CGB_ERR_UNSUPPORTED, "the merged variant needs the TMA band kernels (stencil problems) and a z-slab / row-block decomposition");
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
   if (c->opts.variant == CGB_VAR_AUTO) {
@@ -643,10 +681,19 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_REQUIRE(c->opts.maxit >= 1 && c->opts.maxit <= c->hist_cap, "maxit %d exceeds the context's hist_cap %d",
               c->opts.maxit, c->hist_cap);
   if (c->opts.spmv_impl == CGB_SPMV_TMA && !c->tma_ok)
-    return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV is not available for this problem (3D stencils only)");
+    return fail(CGB_ERR_UNSUPPORTED, "TMA SpMV is not available for this problem (stencil problems only)");
   if (c->opts.variant == CGB_VAR_PIPELINED) CGB_TRY(ensure_extra(c));
   CGB_TRY(ctx_finalize_peers(c));
   c->stream = pick_stream(c, o->stream);
+  CGB_REQUIRE(c->opts.persistent >= -1 && c->opts.persistent <= 1, "persistent must be -1, 0 or 1");
+  const bool persist_ok = c->opts.variant == CGB_VAR_MERGED2 && cg_persist_supported(c->device);
+  if (c->opts.persistent == 1 && !persist_ok)
+    return fail(CGB_ERR_UNSUPPORTED, "the persistent kernel needs the merged variant and cooperative launch support");
+  c->use_persist = persist_ok && c->opts.persistent != -1;
+  if (c->use_persist) {  // nothing to capture: one cooperative launch runs a whole chunk
+    CGB_CUDA(cg_persist_prepare(c->device));
+    return CGB_OK;
+  }
   if (c->opts.use_graph == 2) {
     cudaGraphExec_t ge;
     const int saved = c->host_cur;
@@ -675,9 +722,12 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
     // r0 = b - A x0: stage x0 as SpMV input (with halos), multiply, then the usual init on the residual
     CGB_CUDA(launch_stage_x0(c->P, c->cfg, c->stream));
     const RankDev& P = c->P;
-    if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.Ap, kSpmvPlain, c->stream));
-    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_h[0], nullptr, nullptr, P.Ap, kSpmvPlain, c->stream));
-    else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.Ap, kSpmvPlain, c->stream));
+    // kSpmvDot, not kSpmvPlain: the all-reduce at its end is the cross-rank barrier that keeps k_init's push of
+    // p0 into the neighbours' exch[0] ghosts from overtaking a neighbour that is still reading x0 there.
+    const int wmode = P.nranks > 1 ? kSpmvDot : kSpmvPlain;
+    if (c->st.kind == CGB_KIND_CSR) CGB_CUDA(launch_spmv_csr(P, c->cfg, P.exch[0], P.Ap, wmode, c->stream));
+    else if (use_tma(c)) CGB_CUDA(launch_spmv_tma(P, c->device, c->tmap[0], c->tmap_h[0], nullptr, nullptr, P.Ap, wmode, c->stream));
+    else CGB_CUDA(launch_spmv_simple(P, c->cfg, P.exch[0], P.Ap, wmode, c->stream));
     c->launches += 2;
   }
   CGB_CUDA(launch_init(c->P, c->cfg, c->opts.tol, c->opts.tol_mode, c->opts.maxit,
@@ -697,6 +747,8 @@ extern "C" int cgb_solve_begin(cgb_ctx* c, const cgb_solve_opts_t* o) {
     c->iters_target = c->opts.maxit + 1;  // the last update only records ||r|| of iteration maxit
   }
   CGB_CUDA(cudaEventRecord(c->ev_begin, c->stream));
+  c->poll_snapshot = Scalars{};
+  c->poll_pending = false;
   c->enqueued = 0;
   c->active = true;
   return CGB_OK;
@@ -708,6 +760,12 @@ extern "C" int cgb_solve_iterate(cgb_ctx* c, int n) {
   if (!c->active) return fail(CGB_ERR_STATE, "cgb_solve_iterate before cgb_solve_begin");
   CGB_CUDA(cudaSetDevice(c->device));
   const int chunk = c->opts.chunk;
+  if (c->use_persist && n > 0) {
+    CGB_TRY(enqueue_persist(c, n, c->stream));
+    c->enqueued += n;
+    c->launches += 1;
+    return CGB_OK;
+  }
   while (n > 0) {
     if (c->opts.use_graph && n >= chunk) {
       cudaGraphExec_t ge;
@@ -734,17 +792,18 @@ extern "C" int cgb_solve_iterate_streamed(cgb_ctx* c, int n, double* host_hist) 
   CGB_REQUIRE(c && host_hist && n >= 0, "cgb_solve_iterate_streamed: bad argument");
   if (!c->active) return fail(CGB_ERR_STATE, "cgb_solve_iterate_streamed before cgb_solve_begin");
   CGB_CUDA(cudaSetDevice(c->device));
-  const int saved_chunk = c->opts.chunk;
-  c->opts.chunk = 1;
+  // plain launches: a graph of length 1 would have to be captured and instantiated here, in the middle of a
+  // solve, while the peers already spin on this rank (see cgb_solve_prepare)
   int rc = CGB_OK;
   for (int i = 0; i < n && rc == CGB_OK; ++i) {
-    rc = cgb_solve_iterate(c, 1);
+    rc = ctx_enqueue_iteration(c, c->stream);
     if (rc == CGB_OK) {
+      c->enqueued += 1;
+      c->launches += c->use_persist ? 1 : launches_per_iter(c);
       cudaError_t e = cudaMemcpyAsync(host_hist + i, &c->P.ctrl->s.rnorm, sizeof(double), cudaMemcpyDeviceToHost, c->stream);
       if (e != cudaSuccess) rc = fail(CGB_ERR_CUDA, "cudaMemcpyAsync(rnorm): %s", cudaGetErrorString(e));
     }
   }
-  c->opts.chunk = saved_chunk;
   return rc;
 }
 
@@ -760,11 +819,34 @@ extern "C" int cgb_solve_poll(cgb_ctx* c, int wait, cgb_solve_result_t* res) {
   CGB_REQUIRE(c && res, "cgb_solve_poll: NULL argument");
   if (!c->active) return fail(CGB_ERR_STATE, "cgb_solve_poll before cgb_solve_begin");
   CGB_CUDA(cudaSetDevice(c->device));
-  Scalars* slot = &c->h_scal[0];
-  CGB_CUDA(cudaMemcpyAsync(slot, &c->P.ctrl->s, sizeof(Scalars), cudaMemcpyDeviceToHost, c->stream));
-  (void)wait;  // the copy is stream-ordered: the result reflects everything enqueued so far
-  CGB_CUDA(cudaStreamSynchronize(c->stream));
-  fill_result(c, *slot, res);
+  if (wait) {
+    Scalars* slot = &c->h_scal[0];
+    CGB_CUDA(cudaMemcpyAsync(slot, &c->P.ctrl->s, sizeof(Scalars), cudaMemcpyDeviceToHost, c->stream));
+    CGB_CUDA(cudaStreamSynchronize(c->stream));  // stream-ordered: reflects everything enqueued so far
+    c->poll_snapshot = *slot;
+    c->poll_pending = false;
+  } else {
+    // non-blocking: harvest the previous snapshot if its copy has landed, start the next one, and return the
+    // newest completed state (possibly one call old). The host never waits for the GPU here.
+    Scalars* slot = &c->h_scal[2];
+    if (c->poll_pending) {
+      cudaError_t q = cudaEventQuery(c->ev_poll_nb);
+      if (q == cudaSuccess) {
+        c->poll_snapshot = *slot;
+        c->poll_pending = false;
+      } else if (q != cudaErrorNotReady) {
+        return fail(CGB_ERR_CUDA, "cudaEventQuery: %s", cudaGetErrorString(q));
+      } else {
+        cudaGetLastError();
+      }
+    }
+    if (!c->poll_pending) {
+      CGB_CUDA(cudaMemcpyAsync(slot, &c->P.ctrl->s, sizeof(Scalars), cudaMemcpyDeviceToHost, c->stream));
+      CGB_CUDA(cudaEventRecord(c->ev_poll_nb, c->stream));
+      c->poll_pending = true;
+    }
+  }
+  fill_result(c, c->poll_snapshot, res);
   res->device_ms = 0.0;
   return CGB_OK;
 }
@@ -794,6 +876,11 @@ extern "C" int cgb_solve_finish(cgb_ctx* c, cgb_solve_result_t* res) {
 extern "C" int cgb_solve(cgb_ctx* c, const cgb_solve_opts_t* o, cgb_solve_result_t* res) {
   CGB_REQUIRE(c && o && res, "cgb_solve: NULL argument");
   CGB_TRY(cgb_solve_begin(c, o));
+  if (c->opts.use_graph == 2 && c->use_persist) {
+    // the persistent kernel IS the device-side loop: one launch, one synchronise, nothing runs after convergence
+    CGB_TRY(cgb_solve_iterate(c, c->iters_target));
+    return cgb_solve_finish(c, res);
+  }
   if (c->opts.use_graph == 2) {
     cudaGraphExec_t ge;
     CGB_TRY(get_while_graph(c, &ge));

@@ -36,13 +36,16 @@ struct cgb_ctx {
   cgb::LaunchCfg cfg{};
 
   cudaStream_t own_stream = nullptr;
-  cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_poll[2] = {nullptr, nullptr};
-  cgb::Scalars* h_scal = nullptr;  // pinned: 2 polling slots
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr, ev_poll[2] = {nullptr, nullptr}, ev_poll_nb = nullptr;
+  cgb::Scalars* h_scal = nullptr;  // pinned: 2 polling slots of cgb_solve + 1 of the non-blocking cgb_solve_poll
   int poll_slot = 0;
+  cgb::Scalars poll_snapshot{};    // newest completed state seen by cgb_solve_poll
+  bool poll_pending = false;       // a non-blocking poll copy is in flight (h_scal[2], ev_poll_nb)
 
   // per-solve state
   cgb_solve_opts_t opts{};
   bool active = false;
+  bool use_persist = false;  // this solve runs on the persistent cooperative kernel (merged variant)
   cudaStream_t stream = nullptr;
   int enqueued = 0;
   int host_cur = 0;      // exchange buffer holding the SpMV input of the next enqueued iteration

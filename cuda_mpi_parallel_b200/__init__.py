@@ -10,7 +10,7 @@ Layout::
     models/    problems (ref 3x3, Poisson 2D/3D, 27-pt, CSR), CPU oracle, GPU solver classes
     ops/       the hot kernels as standalone ops on torch tensors
     parallel/  partitions, padded layouts, peer-memory fabric bootstrap (torchrun / single process)
-    utils/     in-tree sm_100a build, timing + clock sampling, writers, config/CLI
+    utils/     in-tree sm_100a build (build.py), NVML clock sampling for benchmarks (clocks.py)
 """
 from . import _native
 from .models.problems import Problem

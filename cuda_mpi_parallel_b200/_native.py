@@ -54,7 +54,7 @@ class CpuResult(C.Structure):
 class SolveOpts(C.Structure):
     _fields_ = [("tol", C.c_double), ("tol_mode", C.c_int32), ("maxit", C.c_int32), ("variant", C.c_int32),
                 ("spmv_impl", C.c_int32), ("use_graph", C.c_int32), ("chunk", C.c_int32),
-                ("fixed_iters", C.c_int32), ("warm_start", C.c_int32), ("stream", C.c_void_p)]
+                ("fixed_iters", C.c_int32), ("warm_start", C.c_int32), ("persistent", C.c_int32), ("stream", C.c_void_p)]
 
 
 class SolveResult(C.Structure):
@@ -81,6 +81,7 @@ def _declare(lib):
         "cgb_ref3x3": (None, [P(i32), P(i32), vp, vp, vp, vp]),
         "cgb_rhs_value": (dbl, [P(Stencil), C.c_int, C.c_uint64, i64]),
         "cgb_manufactured_u": (dbl, [P(Stencil), i64]),
+        "cgb_rhs_fill_box": (C.c_int, [P(Stencil), C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
         "cgb_partition_make": (C.c_int, [P(Stencil), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, P(Partition)]),
         "cgb_layout_make": (C.c_int, [P(Stencil), P(Partition), P(Layout)]),
         "cgb_cpu_cg_csr": (C.c_int, [i64, vp, vp, vp, vp, vp, dbl, C.c_int, C.c_int, vp, P(CpuResult)]),
@@ -112,6 +113,7 @@ def _declare(lib):
         "cgb_solve_iterate_streamed": (C.c_int, [vp, C.c_int, vp]),
         "cgb_solve_poll": (C.c_int, [vp, C.c_int, P(SolveResult)]),
         "cgb_solve_finish": (C.c_int, [vp, P(SolveResult)]),
+        "cgb_ctx_set_trace": (C.c_int, [vp, vp, C.c_int]),
         "cgb_ctx_launch_count": (i64, [vp]),
         "cgb_op_scratch_bytes": (C.c_size_t, []),
         "cgb_op_dot": (C.c_int, [vp, vp, i64, vp, vp, vp]),

@@ -157,9 +157,22 @@ class Problem:
         if k == N.RHS_ONES:
             return np.ones(self.n)
         out = np.empty(self.n)
-        st = C.byref(self.stencil)
-        for g in range(self.n):
-            out[g] = L.cgb_rhs_value(st, k, seed, g)
+        N.check(L.cgb_rhs_fill_box(C.byref(self.stencil), k, seed, 0, self.stencil.gy, 0, self.stencil.gz, out.ctypes.data))
+        return out
+
+    def rhs_local(self, part, kind: str = "ones", seed: int = 0, out=None):
+        """One rank's owned box of the generated right-hand side (compact, x fastest), bit-identical to the
+        device generator ``CGSolver.set_rhs(kind, seed)``. ``out``: optional float64 buffer (numpy array or a
+        CPU torch tensor, e.g. pinned) of the box size; a numpy array is returned otherwise."""
+        if self.is_csr:
+            return self.rhs(kind, seed)[part.x0:part.x0 + part.nx]
+        n_local = part.nx * part.ny * part.nz
+        if out is None:
+            out = np.empty(n_local)
+        ptr = out.ctypes.data if isinstance(out, np.ndarray) else out.data_ptr()
+        size = out.size if isinstance(out, np.ndarray) else out.numel()
+        assert size == n_local, f"buffer holds {size} values, the rank owns {n_local}"
+        N.check(N.lib().cgb_rhs_fill_box(C.byref(self.stencil), _RHS[kind], seed, part.y0, part.ny, part.z0, part.nz, ptr))
         return out
 
     def manufactured_solution(self) -> np.ndarray:

@@ -189,13 +189,26 @@ class CGSolver:
         N.check(N.lib().cgb_ctx_set_host_history(self._ctx, C.c_void_p(pinned.data_ptr()), pinned.numel()))
         self._host_hist = pinned
 
+    def set_trace(self, buf=None) -> None:
+        """Per-iteration device timestamps of the persistent kernel (profiling aid): ``buf`` is a CUDA int64 tensor
+        with 4 entries per iteration (ns of %globaltimer: p.Ap barrier reached / alpha released / r.r barrier
+        reached / beta released), or None to switch off. Call before begin()/solve()."""
+        if buf is None:
+            N.check(N.lib().cgb_ctx_set_trace(self._ctx, None, 0))
+            self._trace = None
+            return
+        assert buf.is_cuda and buf.element_size() == 8 and buf.is_contiguous()
+        N.check(N.lib().cgb_ctx_set_trace(self._ctx, C.c_void_p(buf.data_ptr()), buf.numel() // 4))
+        self._trace = buf
+
     def history(self, n: int) -> np.ndarray:
         h = np.zeros(max(n, 0))
         N.check(N.lib().cgb_ctx_get_history(self._ctx, h.ctypes.data, int(n)))
         return h
 
     # ---- solve --------------------------------------------------------------------------
-    def _fill_opts(self, tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start=False):
+    def _fill_opts(self, tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start=False,
+                   persistent=None):
         o = self._opts
         o.tol = tol
         o.maxit = maxit
@@ -206,15 +219,19 @@ class CGSolver:
         o.chunk = chunk
         o.fixed_iters = fixed_iters
         o.warm_start = int(bool(warm_start))
+        o.persistent = 0 if persistent is None else (1 if persistent else -1)
         o.stream = self._stream(stream)
         return o
 
     def solve(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "auto",
               spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0,
-              stream=None, warm_start: bool = False) -> SolveResult:
+              stream=None, warm_start: bool = False, persistent=None) -> SolveResult:
         """warm_start: start from the x the solver holds (``set_x0`` / ``load_checkpoint`` / the previous solve)
-        instead of the reference's x0 = 0: r0 = b - A x0."""
-        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start)
+        instead of the reference's x0 = 0: r0 = b - A x0.
+        persistent (merged variant): None = one persistent cooperative kernel per chunk where supported,
+        True = require it, False = two kernels per iteration."""
+        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start,
+                            persistent)
         r = N.SolveResult()
         N.check(N.lib().cgb_solve(self._ctx, C.byref(o), C.byref(r)))
         return SolveResult(r.iters, r.status, r.r0norm, r.rnorm, r.device_ms, r.launches)
@@ -222,15 +239,16 @@ class CGSolver:
     # Split-phase API (bench.py times `iterate` between CUDA events on the caller's stream).
     def begin(self, tol: float = 1e-7, maxit: int = 2000, tol_mode: str = "abs", variant: str = "auto",
               spmv: str = "auto", use_graph: bool = True, chunk: int = 25, fixed_iters: int = 0, stream=None,
-              warm_start: bool = False):
-        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start)
+              warm_start: bool = False, persistent=None):
+        o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start,
+                            persistent)
         N.check(N.lib().cgb_solve_begin(self._ctx, C.byref(o)))
 
     def prepare(self, **kw):
         """Allocate and capture everything `begin(**kw)` would, without launching. Needed only when one
         host thread drives several ranks (see cgb_solve_prepare)."""
         args = dict(tol=1e-7, maxit=2000, tol_mode="abs", variant="auto", spmv="auto", use_graph=True, chunk=25,
-                    fixed_iters=0, stream=None, warm_start=False)
+                    fixed_iters=0, stream=None, warm_start=False, persistent=None)
         args.update(kw)
         o = self._fill_opts(**args)
         N.check(N.lib().cgb_solve_prepare(self._ctx, C.byref(o)))

@@ -80,6 +80,9 @@ typedef enum cgb_rhs_kind {
 /* Host generators: value of b / of the manufactured solution at a global linear index. */
 double cgb_rhs_value(const cgb_stencil_t* st, int rhs_kind, uint64_t seed, int64_t gidx);
 double cgb_manufactured_u(const cgb_stencil_t* st, int64_t gidx);
+/* Fill `out` (gx*ny*nz doubles, x fastest) with the generated RHS of the box of full rows [y0,y0+ny) x [z0,z0+nz):
+ * bit-identical to what cgb_ctx_set_rhs_generated produces on the device for the same (kind, seed). */
+int cgb_rhs_fill_box(const cgb_stencil_t* st, int rhs_kind, uint64_t seed, int y0, int ny, int z0, int nz, double* out);
 
 /* ---- topology layer (absent in the reference: cudaSetDevice(0), CUDACG.cu:87) ---- */
 
@@ -146,12 +149,13 @@ typedef struct cgb_ctx cgb_ctx;
 typedef enum cgb_variant {
   CGB_VAR_FUSED = 0,      /* classic CG, 3 fused kernels/iter (spmv+dot, update+dot, p-update+halo) */
   CGB_VAR_MERGED = 1,     /* classic CG "recompute": Ap is never stored, the x/r update re-evaluates the
-                             stencil from TMA slabs of p (72 instead of 88 B/DOF); 3D stencils, nx <= 512 */
+                             stencil from TMA slabs of p (72 instead of 88 B/DOF); any stencil problem (rows wider than
+                             one tile are cut into x tiles) */
   CGB_VAR_PIPELINED = 2,  /* Ghysels-Vanroose, one fused 2-scalar reduction per iteration */
   CGB_VAR_AUTO = 3,       /* fastest measured variant that applies: MERGED2, else MERGED, else FUSED */
   CGB_VAR_MERGED2 = 4     /* classic CG, 2 kernels/iter, 64 B/DOF: p = r + beta p folded into the SpMV (halo rows
                              recomputed in shared memory, boundary planes pushed first) + the MERGED update
-                             kernel; 3D stencils, nx <= 512, z-slab decomposition */
+                             kernel; any stencil problem, z-slab (2D: row-block) decomposition */
 } cgb_variant;
 
 typedef enum cgb_spmv_impl {
@@ -174,6 +178,10 @@ typedef struct cgb_solve_opts_t {
   int32_t warm_start;    /* 0: x0 = 0 like the reference (CUDACG.cu:177-179, 247); 1: start from the x the
                             context holds (cgb_ctx_set_x0 or the previous solve): r0 = b - A x0. This is
                             also the restart path of a checkpoint (x + iteration count). */
+  int32_t persistent;    /* merged variant only. 0 (default): run the iteration loop inside ONE persistent cooperative
+                            kernel per chunk when the device supports cooperative launch - grid barrier and all-reduce
+                            on the device, no kernel boundary inside an iteration; 1: require it; -1: two kernels per
+                            iteration (captured in graphs) as in use_graph */
   void* stream;          /* cudaStream_t to run on; NULL = context stream */
 } cgb_solve_opts_t;
 void cgb_solve_opts_default(cgb_solve_opts_t* o);
@@ -245,10 +253,17 @@ int cgb_ctx_set_host_history(cgb_ctx* c, double* pinned, int cap);
  * host_hist[i] (pinned memory): the reference's per-iteration residual read-back (CUDACG.cu:328)
  * without stalling the host. */
 int cgb_solve_iterate_streamed(cgb_ctx* c, int n, double* host_hist);
-/* wait != 0: synchronise the stream first. Fills res from device-resident state. */
+/* wait != 0: stream-ordered snapshot of the device state, host blocks until it has landed.
+ * wait == 0: never blocks: returns the newest snapshot whose copy has completed (zeros before the first one
+ * lands) and starts the next copy; a host loop can poll between chunks without serialising with the GPU. */
 int cgb_solve_poll(cgb_ctx* c, int wait, cgb_solve_result_t* res);
 /* Finalise x for variants that defer the last update; must follow the last iterate. */
 int cgb_solve_finish(cgb_ctx* c, cgb_solve_result_t* res);
+/* Profiling aid (the reference has no timing at all; its cpuSecond(), CUDACG.cu:35-39, is never called): the
+ * persistent kernel stores four %globaltimer readings (ns) per iteration into dev_buf[4*iter .. 4*iter+3] - last CTA
+ * reached the p.Ap barrier, alpha released, last CTA reached the r.r barrier, beta released - which splits an
+ * iteration into compute and rendezvous time. dev_buf: device memory for 4*cap_iters u64, or NULL to switch off. */
+int cgb_ctx_set_trace(cgb_ctx* c, unsigned long long* dev_buf, int cap_iters);
 /* Kernels launched by this context so far (what bench.py reports as gpu_launches). */
 int64_t cgb_ctx_launch_count(cgb_ctx* c);
 

@@ -76,8 +76,10 @@ def test_maxit_and_fixed_iters_and_rel_tolerance():
     assert r.status == 2 and r.iters == 10
     r = s.solve(fixed_iters=33, chunk=10, variant="fused")
     assert r.iters == 33 and r.launches == 1 + 3 * 33
-    r = s.solve(fixed_iters=33, chunk=10, variant="merged")
+    r = s.solve(fixed_iters=33, chunk=10, variant="merged", persistent=False)
     assert r.iters == 33 and r.launches == 1 + 2 * 33
+    r = s.solve(fixed_iters=33, chunk=10, variant="merged", persistent=True)   # one cooperative launch per chunk
+    assert r.iters == 33 and r.launches == 1 + 4
     r = s.solve(tol=1e-6, tol_mode="rel", maxit=5000)
     assert r.status == 1 and r.rnorm < 1e-6 * r.r0norm
 
@@ -149,21 +151,42 @@ def test_recompute_variant_rejects_unsupported_problems():
 @pytest.mark.parametrize("prob", [Problem.poisson3d(40, 36, 44), Problem.poisson3d(130, 37, 21), Problem.stencil27(24, 28, 24),
                                   Problem.poisson3d(512, 24, 20), Problem.poisson3d(384, 20, 9), Problem.poisson3d(33, 5, 3)],
                          ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
-def test_merged_variant_matches_oracle(prob):
-    # 64 B/DOF variant: p-update folded into the SpMV (halo rows recomputed in shared memory).
+@pytest.mark.parametrize("persistent", [True, False], ids=["persistent", "two-kernel"])
+def test_merged_variant_matches_oracle(prob, persistent):
+    # 64 B/DOF variant: p-update folded into the SpMV (halo rows recomputed in shared memory); either as ONE
+    # persistent cooperative kernel per chunk (grid barrier + reduction on the device) or as two kernels per iteration.
     b = prob.rhs("random", seed=19)
     ref = cpu_cg(prob, b, tol=1e-8)
     s = CGSolver(prob)
     s.set_rhs(b)
-    res = s.solve(tol=1e-8, variant="merged", chunk=5)
+    res = s.solve(tol=1e-8, variant="merged", chunk=5, persistent=persistent)
     assert res.status == 1 and abs(res.iters - ref.iters) <= 1
     n = min(res.iters, ref.iters)
     h = s.history(n)
     big = ref.history[:n] > 1e-6 * ref.r0norm
     np.testing.assert_allclose(h[big], ref.history[:n][big], rtol=1e-8)
     np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
-    r2 = s.solve(tol=1e-8, variant="merged", chunk=4, use_graph=False)     # repeat on the same context
+    r2 = s.solve(tol=1e-8, variant="merged", chunk=4, use_graph=False, persistent=persistent)     # repeat on the same context
     assert r2.iters == res.iters and (s.history(n) == h).all()
+    r3 = s.solve(tol=1e-8, variant="merged", chunk=7, persistent=not persistent)     # the other driver: same arithmetic
+    assert r3.iters == res.iters
+    np.testing.assert_allclose(s.history(n), h, rtol=1e-12)
+
+
+@pytest.mark.parametrize("prob", [Problem.poisson3d(64, 64, 64), Problem.poisson2d(300, 200), Problem.stencil27(32, 32, 32)],
+                         ids=lambda p: p.name)
+def test_persistent_kernel_single_launch_whole_solve(prob):
+    # use_graph="while" on the persistent path = ONE kernel launch for the whole solve (plus the init kernel)
+    b = prob.rhs("random", seed=3)
+    ref = cpu_cg(prob, b, tol=1e-8)
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(tol=1e-8, variant="merged", use_graph="while", persistent=True)
+    assert res.status == 1 and abs(res.iters - ref.iters) <= 1 and res.launches == 2
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6)
+    odd = s.solve(fixed_iters=7, variant="merged", chunk=3, persistent=True)    # odd chunks: entry parity alternates
+    assert odd.iters == 7
+    np.testing.assert_allclose(s.history(7), ref.history[:7], rtol=1e-8)
 
 
 @pytest.mark.parametrize("variant,prob", [("fused", Problem.poisson2d(150, 110)), ("fused", Problem.stencil27(24, 20, 28)),
