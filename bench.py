@@ -132,9 +132,9 @@ def main():
         if (ts > 0).all() and K > 2:
             import numpy as np
             mine = {"rank": rank,
-                    "phaseA_us": float(np.median(ts[1:, 0] - ts[:-1, 3])), "rendezvousA_us": float(np.median(ts[:, 1] - ts[:, 0])),
-                    "phaseB_us": float(np.median(ts[:, 2] - ts[:, 1])), "rendezvousB_us": float(np.median(ts[:, 3] - ts[:, 2])),
-                    "iteration_us": float(np.median(ts[1:, 3] - ts[:-1, 3]))}
+                    "phaseA_us": float(np.median(ts[1:, 0] - ts[:-1, 2])), "alpha_latency_us": float(np.median(ts[:, 1] - ts[:, 0])),
+                    "phaseB_us": float(np.median(ts[:, 2] - ts[:, 0])), "beta_latency_us": float(np.median(ts[:, 3] - ts[:, 2])),
+                    "iteration_us": float(np.median(ts[1:, 2] - ts[:-1, 2]))}
         else:
             mine = {"rank": rank, "note": "no persistent-kernel timestamps (variant without the persistent kernel?)"}
         budget = [mine]
@@ -198,9 +198,9 @@ def main():
             "clocks": clk.summary(), "e2e": e2e, "gpu_launches": int(launches), "impl": "ours",
         }
         if budget is not None:
-            # phase = from the release of the previous barrier to the arrival of this rank's last CTA (compute + skew
-            # inside the rank); rendezvous = from that arrival to the release (partial sum, all-reduce over NVLink,
-            # i.e. waiting for the slowest rank, scalar update)
+            # phaseA/phaseB = from one local grid barrier to the next (all working CTAs of the rank arrived), as seen by the
+            # service CTA; alpha/beta latency = from that barrier to the publication of the scalars (partial sum, all-reduce
+            # over NVLink = waiting for the slowest rank, scalar update) - time the working CTAs spend loading the next phase
             out["iteration_budget_us"] = budget
         print(json.dumps(out))
     if world > 1:

@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(kThreads) k_init(const __grid_constant__ RankD
   const cgb_layout_t& L = P.lay;
   const u64 version = S.halo_seq + 1;
   if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-  __syncthreads();
+  block_sync();
   double* __restrict__ p = P.exch[0];
   const UnitMap um{(L.nx + 1) / 2, L.ny};
   const unsigned stride = gridDim.x * kThreads;
@@ -112,7 +112,7 @@ __global__ void __launch_bounds__(kThreads) k_stage_x0(const __grid_constant__ R
   const cgb_layout_t& L = P.lay;
   const u64 version = S.halo_seq + 1;
   if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-  __syncthreads();
+  block_sync();
   double* __restrict__ p = P.exch[0];
   const UnitMap um{(L.nx + 1) / 2, L.ny};
   const unsigned stride = gridDim.x * kThreads;
@@ -401,7 +401,7 @@ __global__ void __launch_bounds__(kThreads) k_pupdate(const __grid_constant__ Ra
   const unsigned tid0 = blockIdx.x * kThreads + threadIdx.x;
   if (P.nbr_mask) {
     if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-    __syncthreads();
+    block_sync();
     const BRows B = brows_make(L);
     const unsigned UA = (unsigned)B.total * (unsigned)um.pw;
     for (unsigned u = tid0; u < UA; u += stride) {
@@ -451,12 +451,12 @@ __global__ void __launch_bounds__(kThreads) k_pupdate(const __grid_constant__ Ra
     // distributed CSR has no geometric halo: the last CTA tells every rank that this rank's rows of
     // the new p are in memory; the peers' SpMV then loads what it needs by index
     __shared__ int s_last;
-    __syncthreads();
+    block_sync();
     if (threadIdx.x == 0) {
       __threadfence();
       s_last = atomicAdd(&S.ticket_red, 1u) == gridDim.x - 1;
     }
-    __syncthreads();
+    block_sync();
     if (s_last) {
       if (threadIdx.x == 0) S.ticket_red = 0u;
       ready_publish(P, version);

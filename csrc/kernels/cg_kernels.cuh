@@ -50,8 +50,9 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const map
                              int newbuf, cudaStream_t s);
 // Persistent cooperative kernel: `niter` whole iterations of the merged variant in one launch (grid barrier +
 // all-reduce on the device). maps: r with halo rows, exch[0], exch[1], their three halo-box twins, x, r (band rows).
-cudaError_t launch_cg_persist(const RankDev& P, int device, const void* const maps[8], int cur, int niter,
-                              cudaStream_t s);
+cudaError_t launch_cg_persist(const RankDev& P, int device, const void* d_maps, int cur, int niter, cudaStream_t s);
+size_t cg_persist_maps_bytes();                                            // size of the device-resident map block
+cudaError_t cg_persist_upload_maps(void* d_maps, const void* const maps[8]);  // host maps -> device block (synchronous)
 bool cg_persist_supported(int device);
 cudaError_t cg_persist_prepare(int device);  // one-time per-device set-up (allocates): call from the prepare path
 cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* in, double* out, int mode,

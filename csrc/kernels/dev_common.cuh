@@ -41,6 +41,7 @@ struct Scalars {
   u64 red_seq;       // sequence number of the next all-reduce this rank will publish
   u64 halo_seq;      // version of the newest halo this rank has pushed / expects
   u64 gbar;          // persistent kernel: generation of the last completed grid barrier (never reset by a solve)
+  u64 sbar;          // persistent kernel: generation of the last reduction whose scalars have been published
   long long timeout_cycles;
   int tol_mode;
   int iter;          // completed iterations
@@ -49,6 +50,7 @@ struct Scalars {
   int cur;           // pipelined CG: exchange buffer that holds the current w (diagnostic)
   unsigned int ticket_red;
   unsigned int ticket_halo[CGB_NDIR];
+  int dbg[16];       // post-mortem of a timed-out wait: site code, block, thread, ... (cgb_ctx_debug_print)
 };
 
 // Peers write red_ll and halo_flag with P2P stores; everything from `s` on is rank-local.
@@ -88,6 +90,7 @@ struct RankDev {
   // alpha released, last CTA reached barrier B, beta released. Gives the compute / rendezvous split of an iteration.
   unsigned long long* trace;
   int trace_cap;      // iterations the buffer can hold
+  int dbg_flags;      // CGB_DEBUG_FLAGS: bit 0 = no phase-A prologue prefetch in the persistent kernel
   double2* partials;
   // CSR problems
   const int* csr_rowptr;
@@ -164,6 +167,15 @@ __device__ __forceinline__ bool spin_until_ge(const u64* p, u64 target, long lon
   }
 }
 
+// __syncthreads() is an ALIGNED barrier: each warp has to execute it converged. After a block that only some lanes
+// run (if (threadIdx.x == 0) ..., if (lane == 0) ...) ptxas usually - but not always - reconverges the warp first;
+// where it does not, the lanes that skipped the block run through the barrier ahead of the others (observed in
+// the persistent CG kernel). block_sync() makes the reconvergence explicit.
+__device__ __forceinline__ void block_sync() {
+  __syncwarp();
+  __syncthreads();
+}
+
 // ---- deterministic reductions ----
 
 __device__ __forceinline__ double warp_sum(double v) {
@@ -180,12 +192,12 @@ __device__ __forceinline__ void block_sum2_t(double& a, double& b, double* smem)
   a = warp_sum(a);
   b = warp_sum(b);
   const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-  __syncthreads();  // smem reuse guard
+  block_sync();  // smem reuse guard
   if (l == 0) {
     smem[w] = a;
     smem[32 + w] = b;
   }
-  __syncthreads();
+  block_sync();
   if (w == 0) {
     a = l < NW ? smem[l] : 0.0;
     b = l < NW ? smem[32 + l] : 0.0;
@@ -208,7 +220,7 @@ __device__ __forceinline__ bool grid_sum2_last_t(double& a, double& b, double2* 
     unsigned int t = atomicAdd(ticket, 1u);
     s_last = (t == gridDim.x - 1);
   }
-  __syncthreads();
+  block_sync();
   if (!s_last) return false;
   __threadfence();
   double sa = 0.0, sb = 0.0;
@@ -246,13 +258,13 @@ __device__ __forceinline__ bool allreduce2_last_cta(const RankDev& P, double& a,
   __shared__ int s_ok;
   const u64 seq = S.red_seq;
   const int slot = (int)(seq & (kRedSlots - 1));
-  __syncthreads();
+  block_sync();
   if (threadIdx.x == 0) {
     smem[0] = a;
     smem[1] = b;
     s_ok = 1;
   }
-  __syncthreads();
+  block_sync();
   const int t = threadIdx.x;
   const unsigned tag = (unsigned)(seq + 1);
   if (t < P.nranks) {
@@ -262,7 +274,7 @@ __device__ __forceinline__ bool allreduce2_last_cta(const RankDev& P, double& a,
     smem[16 + 2 * t] = va;
     smem[17 + 2 * t] = vb;
   }
-  __syncthreads();
+  block_sync();
   if (threadIdx.x == 0) {
     double sa = 0.0, sb = 0.0;
     for (int q = 0; q < P.nranks; ++q) {
@@ -285,15 +297,15 @@ __device__ __forceinline__ void allreduce2_publish(const RankDev& P, double a, d
   Scalars& S = P.ctrl->s;
   const u64 seq = S.red_seq;
   const int slot = (int)(seq & (kRedSlots - 1));
-  __syncthreads();
+  block_sync();
   if (threadIdx.x == 0) {
     smem[0] = a;
     smem[1] = b;
   }
-  __syncthreads();
+  block_sync();
   const int t = threadIdx.x;
   if (t < P.nranks) ll_send2(&P.peer_ctrl[t]->red_ll[slot][P.rank][0], smem[0], smem[1], (unsigned)(seq + 1));
-  __syncthreads();
+  block_sync();
   if (threadIdx.x == 0) {
     S.pub_seq = seq;
     S.red_seq = seq + 1;
@@ -306,7 +318,7 @@ __device__ __forceinline__ bool allreduce2_consume(const RankDev& P, u64 seq, do
   __shared__ int s_cok;
   const int slot = (int)(seq & (kRedSlots - 1));
   if (threadIdx.x == 0) s_cok = 1;
-  __syncthreads();
+  block_sync();
   const int t = threadIdx.x;
   if (t < P.nranks) {
     double va, vb;
@@ -314,7 +326,7 @@ __device__ __forceinline__ bool allreduce2_consume(const RankDev& P, u64 seq, do
     smem[2 * t] = va;
     smem[2 * t + 1] = vb;
   }
-  __syncthreads();
+  block_sync();
   double sa = 0.0, sb = 0.0;
   for (int q = 0; q < P.nranks; ++q) {
     sa += smem[2 * q];
@@ -323,7 +335,7 @@ __device__ __forceinline__ bool allreduce2_consume(const RankDev& P, u64 seq, do
   a = sa;
   b = sb;
   const bool ok = s_cok != 0;
-  __syncthreads();
+  block_sync();
   return ok;
 }
 
@@ -357,13 +369,13 @@ __device__ __forceinline__ void cg_after_rr(const RankDev& P, double rr) {
 // Called by all threads of a CTA after it stored `cnt[d]` units into neighbour d's ghost layer.
 // The CTA that completes direction d raises the neighbour's flag with `version`.
 __device__ __forceinline__ void halo_commit(const RankDev& P, const unsigned* cnt_smem, u64 version) {
-  __syncthreads();  // counters complete
+  block_sync();  // counters complete
   unsigned any = 0;
 #pragma unroll
   for (int d = 0; d < CGB_NDIR; ++d) any |= cnt_smem[d];
   if (!any) return;        // CTA-uniform: this CTA pushed nothing
   __threadfence_system();  // my remote stores are performed before the counters move
-  __syncthreads();
+  block_sync();
   const int d = threadIdx.x;
   if (d < CGB_NDIR && d != 4 && cnt_smem[d] != 0 && P.nbr[d] >= 0) {
     Scalars& S = P.ctrl->s;
@@ -381,7 +393,7 @@ __device__ __forceinline__ void halo_commit(const RankDev& P, const unsigned* cn
 __device__ __forceinline__ bool halo_wait_all(const RankDev& P, u64 version) {
   __shared__ int s_hok;
   if (threadIdx.x == 0) s_hok = 1;
-  __syncthreads();
+  block_sync();
   const int d = threadIdx.x;
   if (d < CGB_NDIR && d != 4 && P.nbr[d] >= 0) {
     if (!spin_until_ge(&P.ctrl->halo_flag[d], version, P.ctrl->s.timeout_cycles)) {
@@ -389,7 +401,7 @@ __device__ __forceinline__ bool halo_wait_all(const RankDev& P, u64 version) {
       P.ctrl->s.done = CGB_ERR_TIMEOUT;
     }
   }
-  __syncthreads();
+  block_sync();
   return s_hok != 0;
 }
 
@@ -417,12 +429,12 @@ __device__ __forceinline__ void ready_publish(const RankDev& P, u64 version) {
 __device__ __forceinline__ bool ready_wait(const RankDev& P, u64 version) {
   __shared__ int s_rok;
   if (threadIdx.x == 0) s_rok = 1;
-  __syncthreads();
+  block_sync();
   if ((int)threadIdx.x < P.nranks && !spin_until_ge(&P.ctrl->ready_flag[threadIdx.x], version, P.ctrl->s.timeout_cycles)) {
     s_rok = 0;
     P.ctrl->s.done = CGB_ERR_TIMEOUT;
   }
-  __syncthreads();
+  block_sync();
   return s_rok != 0;
 }
 

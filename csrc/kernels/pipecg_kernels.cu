@@ -27,7 +27,7 @@ __device__ __forceinline__ void for_pairs_boundary_first(const RankDev& P, unsig
   const unsigned tid0 = blockIdx.x * kThreads + threadIdx.x;
   if (P.nbr_mask) {
     if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-    __syncthreads();
+    block_sync();
     const BRows B = brows_make(L);
     const unsigned UA = (unsigned)B.total * (unsigned)um.pw;
     for (unsigned u = tid0; u < UA; u += stride) {

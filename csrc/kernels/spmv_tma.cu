@@ -68,7 +68,9 @@ struct BandGeo {
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+  // "memory": without it the compiler is free to sink the init below the __syncthreads() that publishes it (seen
+  // with the persistent kernel: the TMA lane armed barriers that thread 0 had not initialised yet)
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -76,18 +78,57 @@ __device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+// Wait for a phase of an mbarrier. Bounded like every other wait of this library: if the phase does not complete
+// within the peer-wait timeout (a lost TMA transaction, a dead producer), the solve is failed with
+// CGB_ERR_TIMEOUT and the wait - and every later one, which sees the failed state after its first unsuccessful
+// try - falls through, so the kernel drains instead of hanging. `site` lands in Scalars::dbg for the post-mortem.
+__device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
+  unsigned ok;
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
       : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity, Scalars& S, int site) {
+  if (mbar_try(bar, parity)) return;
+  const long long t0 = clock64();
+  unsigned spins = 0;
+  while (!mbar_try(bar, parity)) {
+    if ((++spins & 0xffu) != 0) continue;   // look at the clock and the failure flag only now and then
+    if (*(volatile int*)&S.done == CGB_ERR_TIMEOUT) return;
+    if (clock64() - t0 > 4 * S.timeout_cycles) {
+      if (atomicCAS(&S.dbg[0], 0, site) == 0) {  // the first wait that gave up tells the story
+        S.dbg[1] = (int)blockIdx.x;
+        S.dbg[2] = (int)threadIdx.x;
+        S.dbg[3] = (int)bar;
+        S.dbg[4] = (int)parity;
+        S.dbg[5] = (int)*(volatile u64*)&S.gbar;
+        S.dbg[6] = (int)*(volatile u64*)&S.sbar;
+        // raw state words of this barrier and of its partner array (full <-> empty are 64 bytes apart)
+        unsigned long long w0, w1, w2;
+        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(w0) : "r"(bar));
+        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(w1) : "r"(bar - 64));
+        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(w2) : "r"(bar - 56));
+        S.dbg[8] = (int)w0;  S.dbg[9] = (int)(w0 >> 32);
+        S.dbg[10] = (int)w1; S.dbg[11] = (int)(w1 >> 32);
+        unsigned crank, cn, dsm, tsm;
+        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
+        asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(cn));
+        asm volatile("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dsm));
+        asm volatile("mov.u32 %0, %%total_smem_size;" : "=r"(tsm));
+        S.dbg[12] = (int)crank; S.dbg[13] = (int)cn; S.dbg[14] = (int)dsm; S.dbg[15] = (int)tsm;
+        (void)w2;
+      }
+      S.done = CGB_ERR_TIMEOUT;
+      return;
+    }
+  }
 }
 __device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, int x, int y, int z, unsigned bar) {
   asm volatile(
@@ -315,6 +356,38 @@ __device__ __forceinline__ Item make_item(const RankDev& P, const BandGeo& G, in
   return it;
 }
 
+__device__ __forceinline__ u64 ld_acquire_gpu(const u64* p) {
+  u64 v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(u64* p, u64 v) {
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Persistent kernel: block until the scalars produced by reduction `seq` (alpha, or beta/done/...) have been
+// published by the service CTA. One poller per warp; the rest of the warp waits at the __syncwarp.
+__device__ __forceinline__ void wait_scalars(const RankDev& P, u64 seq) {
+  Scalars& S = P.ctrl->s;
+  if ((threadIdx.x & 31) == 0 && ld_acquire_gpu(&S.sbar) < seq) {
+    const long long t0 = clock64();
+    while (ld_acquire_gpu(&S.sbar) < seq) {
+      if (clock64() - t0 > 4 * S.timeout_cycles) {  // the service CTA's own waits are bounded by timeout_cycles
+        if (atomicCAS(&S.dbg[0], 0, 10) == 0) {
+          S.dbg[1] = (int)blockIdx.x;
+          S.dbg[2] = (int)threadIdx.x;
+          S.dbg[3] = (int)seq;
+          S.dbg[5] = (int)*(volatile u64*)&S.gbar;
+          S.dbg[6] = (int)*(volatile u64*)&S.sbar;
+        }
+        S.done = CGB_ERR_TIMEOUT;
+        break;
+      }
+    }
+  }
+  __syncwarp();
+}
+
 // State of one mbarrier ring: smem addresses of the full/empty barrier arrays and the number of slabs this
 // thread's role has issued (producer lane) or consumed (consumer threads) so far. A persistent kernel keeps
 // one Ring per phase alive across iterations; the per-iteration kernels start one at zero.
@@ -322,6 +395,30 @@ struct Ring {
   unsigned full0, empty0;
   unsigned n;
 };
+
+// Branch-free variant for the persistent kernel: EVERY thread executes the same straight-line code and a predicate
+// selects the one initialising thread, so no warp diverges in front of the __syncthreads() that publishes the
+// barriers (see k_cg_persist for why that matters there).
+__device__ __forceinline__ void mbar_init_if(unsigned bar, unsigned count, bool doit) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.u32 p, %2, 0;\n"
+      "@p mbarrier.init.shared::cta.b64 [%0], %1;\n"
+      "}\n" ::"r"(bar),
+      "r"(count), "r"((unsigned)doit)
+      : "memory");
+}
+__device__ __forceinline__ void ring_init_uniform(unsigned long long* bars, int nstages) {
+  const unsigned full0 = smem_u32(bars), empty0 = smem_u32(bars + kMaxStages);
+#pragma unroll
+  for (int s = 0; s < kMaxStages; ++s) {
+    const bool mine = threadIdx.x == 0 && s < nstages;
+    mbar_init_if(full0 + 8 * s, 1, mine);
+    mbar_init_if(empty0 + 8 * s, kNC / 32, mine);
+  }
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
 
 __device__ __forceinline__ void ring_init(Ring& R, unsigned long long* bars, int nstages) {
   R.full0 = smem_u32(bars);
@@ -343,7 +440,11 @@ template <int KIND, int OUT>
 __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, const CUtensorMap* tmap,
                                            const CUtensorMap* tmap_h, const CUtensorMap* tmx, const CUtensorMap* tmr,
                                            double* __restrict__ out, double alpha, u64 halo_version,
-                                           unsigned char* smem_raw, Ring& R, double& acc) {
+                                           unsigned char* smem_raw, Ring& R, double& acc, bool lazy = false,
+                                           u64 lazy_seq = 0) {
+  // lazy (persistent kernel, OUT == 2): alpha is not known yet when the sweep starts - it is the result
+  // of reduction lazy_seq, still crossing NVLink. The TMA lane does not need it at all and the consumers only
+  // when they emit their first plane, two slabs into the sweep; they pick it up there.
   constexpr int BW = BoxW<KIND>::v;
   Scalars& S = P.ctrl->s;
   // Opaque copies of the thread/block index: in the persistent kernel this keeps everything derived from them
@@ -381,7 +482,7 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
           const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
           if ((q == -1 && nb_zlo) || (q == L.nz && nb_zhi)) wait_flags();
           const unsigned st = n % kStages, ph = (n / kStages) & 1u;
-          mbar_wait(empty0 + 8 * st, ph ^ 1u);
+          mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 1);
           const bool with_xr = OUT == 2 && s >= 2;  // this step emits a plane: bring its x and r rows too
           mbar_expect_tx(full0 + 8 * st, p_tx + (with_xr ? 2u * (unsigned)G.xr_bytes : 0u));
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
@@ -423,7 +524,7 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
       Run2 A{}, B{};
       for (int s = 0; s < nsteps; ++s, ++n) {
         const unsigned st = n % kStages, ph = (n / kStages) & 1u;
-        mbar_wait(full0 + 8 * st, ph);
+        mbar_wait(full0 + 8 * st, ph, S, 2);
         const unsigned char* stage = smem_raw + (size_t)st * G.stage_bytes;
         PS2 na{}, nb{};
         if (active) plane_from_slab<KIND>(stage, tp, ra, na, nb);
@@ -443,6 +544,11 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
         if (s >= 2) {
+          if (OUT == 2 && lazy) {
+            wait_scalars(P, lazy_seq);
+            alpha = __ldcg(&S.alpha);
+            lazy = false;
+          }
           if (va) emit<KIND, OUT>(P, out, A, ta, idx, pair, alpha, cxa, cra, acc);
           if (vb) emit<KIND, OUT>(P, out, B, tb, idx + L.pitch, pair, alpha, cxb, crb, acc);
           idx += ps;
@@ -470,7 +576,7 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
   if (S.done != 0) return;
   Ring R;
   ring_init(R, bars, G.nstages);
-  __syncthreads();
+  block_sync();
   double acc = 0.0;
   phase_spmv<KIND, OUT>(P, G, &tmap, &tmap_h, &tmx, &tmr, out, S.alpha, S.halo_seq, smem_raw, R, acc);
   if (mode == kSpmvPlain) return;
@@ -509,7 +615,8 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
                                             const CUtensorMap* tm_r_h, const CUtensorMap* tm_pold_h,
                                             const CUtensorMap* tm_pnew_h, const double* pold, double* pnew, int newbuf,
                                             double beta, u64 version, unsigned* cnt, unsigned char* smem_raw, Ring& R,
-                                            double& acc) {
+                                            double& acc, bool lazy = false, u64 lazy_seq = 0,
+                                            int* done_seen = nullptr) {
   constexpr int BW = BoxW<KIND>::v;
   Scalars& S = P.ctrl->s;
   unsigned tid = threadIdx.x, bid = blockIdx.x;  // opaque copies, see phase_spmv
@@ -518,6 +625,55 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
   const unsigned kStages = (unsigned)G.nstages;
   const cgb_layout_t& L = P.lay;
   const bool nb_zlo = P.nbr[dir_index(0, -1)] >= 0, nb_zhi = P.nbr[dir_index(0, 1)] >= 0;
+  const int boxb = G.prow * BW * 8;
+  unsigned n = R.n;
+
+  // One slab (r or ghost p_new, plus p_old) of step s of an item into its ring stage. TMA lane only.
+  auto issue = [&](const Item& it, int s, unsigned nn) {
+    const int y0 = it.yb * G.RB;
+    const unsigned p_tx = (unsigned)(G.NBX * boxb + (G.ntx > 1 ? 2 * G.prow * 16 : 0));
+    const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
+    const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
+    const unsigned st = nn % kStages, ph = (nn / kStages) & 1u;
+    mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 1000 + (int)nn);
+    mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
+    const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
+    for (int b = 0; b < G.NBX; ++b) {
+      tma_load_3d(dst + b * boxb, ghost ? tm_pnew : tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+      tma_load_3d(dst + G.p_bytes + b * boxb, tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+    }
+    if (G.ntx > 1) {
+      const int xl = it.x0 - 2, xr = it.x0 + 2 * G.LX;
+      tma_load_3d(dst + G.h_off, ghost ? tm_pnew_h : tm_r_h, xl, y0, q + 1, full0 + 8 * st);
+      tma_load_3d(dst + G.h_off + 128, ghost ? tm_pnew_h : tm_r_h, xr, y0, q + 1, full0 + 8 * st);
+      tma_load_3d(dst + G.p_bytes + G.h_off, tm_pold_h, xl, y0, q + 1, full0 + 8 * st);
+      tma_load_3d(dst + G.p_bytes + G.h_off + 128, tm_pold_h, xr, y0, q + 1, full0 + 8 * st);
+    }
+  };
+  auto is_ghost_step = [&](const Item& it, int s) {
+    const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
+    return (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
+  };
+
+  // ---- persistent kernel: beta is the result of reduction lazy_seq, which may still be crossing NVLink. The TMA
+  // lane first fills the ring with the opening slabs of its first item (they depend on local data only, which the
+  // grid barrier has made visible), then everybody waits for the scalars. ----
+  int prefetched = 0;
+  if (lazy) {
+    const int item0 = bid < (unsigned)G.nctas ? (int)bid : G.nitems;
+    if (tid == kNC && item0 < G.nitems && !(P.dbg_flags & 1)) {
+      const Item it = make_item(P, G, item0, nb_zlo, nb_zhi, false, false);
+      const int nsteps = it.k1 - it.k0 + 2;
+      while (prefetched < nsteps && prefetched < (int)kStages && !is_ghost_step(it, prefetched)) {
+        issue(it, prefetched, n + (unsigned)prefetched);
+        ++prefetched;
+      }
+    }
+    wait_scalars(P, lazy_seq);
+    beta = __ldcg(&S.beta);
+    version = __ldcg(&S.halo_seq);
+    if (done_seen) *done_seen = __ldcg(&S.done);
+  }
 
   // ---- boundary planes first: push p_new of my first/last plane into the neighbours' ghosts ----
   if (P.nbr_mask) {
@@ -530,7 +686,7 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
     const bool pusher = bid >= (unsigned)G.nctas && bid < (unsigned)(G.nctas + G.nhalo);
     const unsigned first = dedicated ? (pusher ? (bid - G.nctas) * kNT + tid : total)
                                      : bid * kNT + tid;
-    const unsigned step = (dedicated ? (unsigned)G.nhalo : gridDim.x) * kNT;
+    const unsigned step = (dedicated ? (unsigned)G.nhalo : gridDim.x - (lazy ? 1u : 0u)) * kNT;  // lazy: minus the service CTA
     for (unsigned u0 = first; u0 < total; u0 += 4 * step) {  // 4 units in flight per thread
       int64_t src[4], dst[4];
       int dd[4];
@@ -569,42 +725,25 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
   }
 
   const int warp = tid >> 5, lane = tid & 31;
-  const int boxb = G.prow * BW * 8;
-  unsigned n = R.n;
 
   if (warp == kNC / 32) {
     if (lane == 0) {
       bool waited = false;
       for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
-        const int y0 = it.yb * G.RB;
         const int nsteps = it.k1 - it.k0 + 2;
-        const unsigned p_tx = (unsigned)(G.NBX * boxb + (G.ntx > 1 ? 2 * G.prow * 16 : 0));
-        for (int s = 0; s < nsteps; ++s, ++n) {
-          const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
-          const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
-          if (ghost && !waited) {
+        int s = prefetched;   // slabs of the first item that are already in flight
+        n += (unsigned)prefetched;
+        prefetched = 0;
+        for (; s < nsteps; ++s, ++n) {
+          if (is_ghost_step(it, s) && !waited) {
             for (int d = 0; d < CGB_NDIR; ++d)
               if (d != 4 && P.nbr[d] >= 0 && !spin_until_ge(&P.ctrl->halo_flag[d], version, S.timeout_cycles))
                 S.done = CGB_ERR_TIMEOUT;
             asm volatile("fence.proxy.async;" ::: "memory");
             waited = true;
           }
-          const unsigned st = n % kStages, ph = (n / kStages) & 1u;
-          mbar_wait(empty0 + 8 * st, ph ^ 1u);
-          mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
-          const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
-          for (int b = 0; b < G.NBX; ++b) {
-            tma_load_3d(dst + b * boxb, ghost ? tm_pnew : tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + b * boxb, tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
-          }
-          if (G.ntx > 1) {
-            const int xl = it.x0 - 2, xr = it.x0 + 2 * G.LX;
-            tma_load_3d(dst + G.h_off, ghost ? tm_pnew_h : tm_r_h, xl, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.h_off + 128, ghost ? tm_pnew_h : tm_r_h, xr, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + G.h_off, tm_pold_h, xl, y0, q + 1, full0 + 8 * st);
-            tma_load_3d(dst + G.p_bytes + G.h_off + 128, tm_pold_h, xr, y0, q + 1, full0 + 8 * st);
-          }
+          issue(it, s, n);
         }
       }
     }
@@ -631,7 +770,7 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
         const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
         const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
         const bool inb = q >= 0 && q < L.nz;
-        mbar_wait(full0 + 8 * st, ph);
+        mbar_wait(full0 + 8 * st, ph, S, 2000 + (int)n);
         const unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
         double2 pna = make_double2(0, 0), pnb = pna;
         PS2 na{}, nb{};
@@ -686,7 +825,7 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
   Ring R;
   ring_init(R, bars, G.nstages);
   if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-  __syncthreads();
+  block_sync();
   double acc = 0.0;
   phase_pspmv<KIND>(P, G, &tm_r, &tm_pold, &tm_pnew, &tm_r_h, &tm_pold_h, &tm_pnew_h, pold, pnew, newbuf, S.beta,
                     S.halo_seq, cnt, smem_raw, R, acc);
@@ -717,155 +856,242 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
 // next: every thread fences (fence.proxy.async) before it arrives at the barrier and the TMA lane fences
 // again after the acquire.
 // ---------------------------------------------------------------------------------------------
+// The eight tensor maps of a context, in DEVICE memory (written once at context creation): r with halo rows,
+// the two exchange buffers, their 2-column halo-box twins, x and r (band rows). The persistent kernel reads its
+// descriptors from here rather than from its parameter block.
 struct PersistMaps {
   CUtensorMap rh, e[2], rh_h, e_h[2], x, r;
 };
-
-__device__ __forceinline__ u64 ld_acquire_gpu(const u64* p) {
-  u64 v;
-  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_gpu(u64* p, u64 v) {
-  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
+static_assert(sizeof(PersistMaps) == 8 * 128, "PersistMaps layout");
 
 // Loop state of the persistent kernel lives in shared memory (accessed volatile), not in registers: the two
 // phases run at the register limit of a 544-thread CTA (96) and anything carried across them would be
 // spilled inside their inner loops.
 struct PersistState {
-  u64 seq;          // grid-barrier generation (thread 0)
+  u64 seq;          // generation of the last grid barrier this CTA has passed
   unsigned nA, nB;  // slabs issued/consumed so far on the two mbarrier rings
   int it;           // iterations completed by this launch
-  int stop;         // set when the solve is finished (or failed): every thread leaves the loop
+  int stop;         // the solve is finished (or failed): every thread leaves the loop
 };
 
-// Everything the persistent kernel needs, in __constant__ memory (one instance per device; launch_cg_persist
-// refreshes it in stream order before every launch). The phases are out-of-line functions - inlined into the
-// iteration loop they lose ~45 registers to loop-invariant code motion and spill inside their inner loops
-// (measured with ptxas -v) - and an out-of-line function can only keep its operands in the constant bank,
-// like the per-iteration kernels do with their __grid_constant__ parameters, if they live in a __constant__
-// variable rather than in the kernel's parameter block.
-struct PersistConst {
-  RankDev P;
-  PersistMaps M;
-  BandGeo GA, GB;
-};
-__constant__ PersistConst c_pc;
+constexpr int kPersistPartials = 256;  // per-barrier-parity block of per-CTA partials (grid <= SM count < 256)
 
-// phase 0: the sum is p.Ap -> alpha. phase 1: the sum is r.r -> stopping test, beta, halo version.
-__device__ __noinline__ void persist_barrier(double a, volatile PersistState* ps, double* red_smem, int phase) {
-  const RankDev& P = c_pc.P;
+// Local half of a barrier: publish this CTA's partial sum, arrive, and wait until every working CTA of this GPU has
+// arrived - i.e. until everything the phase wrote (p_new, or x and r) is visible. The arriving CTAs do NOT wait
+// for the cross-GPU sum: the service CTA picks the partials up from here (persist_service) and the next phase
+// starts loading at once; its threads wait for the scalars only where they first need them.
+__device__ __forceinline__ void persist_arrive(const RankDev& P, double a, volatile PersistState* ps, double* red_smem,
+                                               int done_seen, bool count_iter) {
   Scalars& S = P.ctrl->s;
   double z = 0.0;
-  asm volatile("fence.proxy.async;" ::: "memory");
-  if (grid_sum2_last_t<kNT>(a, z, P.partials, &S.ticket_red, red_smem)) {
-    unsigned long long t_arrive = 0;
-    const int tslot = S.iter;  // iteration this barrier belongs to (cg_after_rr advances it)
-    if (P.trace && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_arrive));
-    const bool ok = allreduce2_last_cta(P, a, z, red_smem);
-    if (threadIdx.x == 0) {
-      if (phase == 0) {
-        S.pAp = a;
-        S.alpha = S.rho / a;
-      } else if (ok) {
-        cg_after_rr(P, a);
-      }
-      const u64 seq = ps->seq + 1;
-      ps->seq = seq;
-      __threadfence();
-      st_release_gpu(&S.gbar, seq);
-      if (P.trace && tslot < P.trace_cap) {
-        unsigned long long t_rel;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_rel));
-        P.trace[4 * tslot + 2 * phase] = t_arrive;
-        P.trace[4 * tslot + 2 * phase + 1] = t_rel;
-      }
-    }
-  } else if (threadIdx.x == 0) {
+  asm volatile("fence.proxy.async;" ::: "memory");  // my generic-proxy stores vs TMA reads of the next phase
+  block_sum2_t<kNT>(a, z, red_smem);
+  if (threadIdx.x == 0) {
     const u64 seq = ps->seq + 1;
     ps->seq = seq;
-    const long long t0 = clock64();
-    while (ld_acquire_gpu(&S.gbar) < seq) {
-      if (clock64() - t0 > 4 * S.timeout_cycles) {  // the last CTA's own waits are bounded by timeout_cycles
-        S.done = CGB_ERR_TIMEOUT;
-        break;
+    __stcg(&P.partials[(seq & 1) * kPersistPartials + blockIdx.x], make_double2(a, 0.0));
+    __threadfence();
+    const unsigned narrive = gridDim.x - 1;  // everybody but the service CTA
+    if (atomicAdd(&S.ticket_red, 1u) == narrive - 1) {
+      S.ticket_red = 0u;
+      __threadfence();
+      st_release_gpu(&S.gbar, seq);
+    } else {
+      const long long t0 = clock64();
+      while (ld_acquire_gpu(&S.gbar) < seq) {
+        if (clock64() - t0 > 4 * S.timeout_cycles) {
+          if (atomicCAS(&S.dbg[0], 0, 11) == 0) {
+            S.dbg[1] = (int)blockIdx.x;
+            S.dbg[3] = (int)seq;
+            S.dbg[5] = (int)*(volatile u64*)&S.gbar;
+            S.dbg[6] = (int)*(volatile u64*)&S.sbar;
+            S.dbg[7] = (int)*(volatile unsigned*)&S.ticket_red;
+          }
+          S.done = CGB_ERR_TIMEOUT;
+          done_seen = CGB_ERR_TIMEOUT;
+          break;
+        }
       }
     }
+    if (count_iter) ps->it = ps->it + 1;
+    if (done_seen != 0) ps->stop = 1;
   }
-  if (threadIdx.x == 0) {
-    if (phase == 1) ps->it = ps->it + 1;
-    if (__ldcg(&S.done) != 0) ps->stop = 1;
-  }
-  __syncthreads();
+  block_sync();  // reconverges warp 0 before the aligned barrier
 }
 
-// Phase A with the SpMV input (p_old) in exchange buffer CUR; CUR is a template parameter so that the vector
-// and tensor-map addresses stay constant-bank operands.
+// The service CTA (last block of the grid, one warp): for every barrier it waits until all working CTAs have
+// arrived, adds their partials in index order (deterministic), exchanges the rank's sum with every peer through
+// 8-byte flag-in-data P2P stores (rank-ordered sum: bit-identical scalars on all ranks), updates the CG scalars
+// and publishes them (sbar). None of this is on the critical path of the working CTAs, which are already loading
+// the next phase. Replaces the two blocking scalar read-backs of the reference (CUDACG.cu:304, CUDACG.cu:328).
+__device__ __forceinline__ void persist_service(const RankDev& P, int niter) {
+  Scalars& S = P.ctrl->s;
+  const int lane = threadIdx.x;
+  const unsigned nwork = gridDim.x - 1;
+  // sbar, not gbar: the working CTAs may pass their first barrier (and advance gbar) before this CTA has even
+  // started, while sbar only ever moves here. The two are equal whenever no launch is in flight.
+  u64 seq = __ldcg(&S.sbar);
+  bool done = __ldcg(&S.done) != 0;
+  if (done) return;  // the working CTAs leave at once, too
+  for (int it = 0; it < niter; ++it) {
+    for (int phase = 0; phase < 2; ++phase) {
+      ++seq;
+      bool alive = true;
+      if (lane == 0) {
+        const long long t0 = clock64();
+        while (ld_acquire_gpu(&S.gbar) < seq)
+          if (clock64() - t0 > 8 * S.timeout_cycles) {  // the working CTAs are gone (their waits are bounded, too)
+            if (atomicCAS(&S.dbg[0], 0, 12) == 0) {
+              S.dbg[3] = (int)seq;
+              S.dbg[5] = (int)*(volatile u64*)&S.gbar;
+              S.dbg[6] = (int)*(volatile u64*)&S.sbar;
+            }
+            S.done = CGB_ERR_TIMEOUT;
+            alive = false;
+            break;
+          }
+      }
+      if (!__shfl_sync(0xffffffffu, (int)alive, 0)) {
+        // keep the invariant sbar == gbar for the next launch, then give up
+        if (lane == 0) st_release_gpu(&S.sbar, ld_acquire_gpu(&S.gbar));
+        return;
+      }
+      unsigned long long t_local = 0;
+      const int tslot = __ldcg(&S.iter);
+      if (P.trace && lane == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_local));
+      double a = 0.0;
+      const double2* part = P.partials + (seq & 1) * kPersistPartials;
+      for (unsigned i = lane; i < nwork; i += 32) a += __ldcg(&part[i]).x;   // fixed order per lane ...
+      a = warp_sum(a);                                                         // ... and a fixed tree across lanes
+      bool ok = true;
+      if (P.nranks > 1) {
+        const u64 rs = S.red_seq;
+        const int slot = (int)(rs & (kRedSlots - 1));
+        const unsigned tag = (unsigned)(rs + 1);
+        double va = 0.0, vb = 0.0;
+        if (lane < P.nranks) {
+          ll_send2(&P.peer_ctrl[lane]->red_ll[slot][P.rank][0], a, 0.0, tag);
+          ok = ll_recv2(&P.ctrl->red_ll[slot][lane][0], tag, S.timeout_cycles, va, vb);
+        }
+        ok = __all_sync(0xffffffffu, ok);
+        a = 0.0;
+        for (int q = 0; q < P.nranks; ++q) a += __shfl_sync(0xffffffffu, va, q);   // rank order on every rank
+      }
+      if (lane == 0) {
+        S.last_sum[0] = a;
+        S.last_sum[1] = 0.0;
+        S.red_seq += 1;
+        if (!ok) {
+          S.done = CGB_ERR_TIMEOUT;
+        } else if (done) {
+          // the speculative p.Ap of a finished solve (see persist_iteration): nothing to update
+        } else if (phase == 0) {
+          S.pAp = a;
+          S.alpha = S.rho / a;
+        } else {
+          cg_after_rr(P, a);
+        }
+        __threadfence();
+        st_release_gpu(&S.sbar, seq);
+        if (P.trace && !done && tslot < P.trace_cap) {
+          unsigned long long t_rel;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_rel));
+          P.trace[4 * tslot + 2 * phase] = t_local;
+          P.trace[4 * tslot + 2 * phase + 1] = t_rel;
+        }
+      }
+      __syncwarp();
+      if (done) return;   // the working CTAs leave after this (speculative) barrier A, too
+      if (phase == 1) done = __shfl_sync(0xffffffffu, lane == 0 ? (int)(S.done != 0) : 0, 0) != 0;
+    }
+  }
+}
+
+// One iteration with the SpMV input in exchange buffer CUR (compile-time, so that the vector and tensor-map
+// addresses stay constant-bank operands of the kernel's parameter block). Returns false when the loop must end.
 template <int KIND, int CUR>
-__device__ __noinline__ double persist_phase_a(volatile PersistState* ps, unsigned long long* bars, unsigned* cnt,
-                                               unsigned char* smem_raw) {
+__device__ __forceinline__ bool persist_iteration(const RankDev& P, const PersistMaps& M, const BandGeo& GA,
+                                                  const BandGeo& GB, int niter, volatile PersistState* ps,
+                                                  unsigned long long* bars, unsigned* cnt, double* red_smem,
+                                                  unsigned char* smem_raw) {
   constexpr int NB = CUR ^ 1;
-  const RankDev& P = c_pc.P;
-  const PersistMaps& M = c_pc.M;
-  Scalars& S = P.ctrl->s;
+  if (ps->stop || ps->it >= niter) return false;
+  if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
+  block_sync();
   if (threadIdx.x == kNC) asm volatile("fence.proxy.async;" ::: "memory");  // TMA lane, after the barrier's acquire
-  Ring R{smem_u32(bars), smem_u32(bars + kMaxStages), ps->nA};
-  double acc = 0.0;
-  phase_pspmv<KIND>(P, c_pc.GA, &M.rh, &M.e[CUR], &M.e[NB], &M.rh_h, &M.e_h[CUR], &M.e_h[NB], P.exch[CUR], P.exch[NB], NB,
-                    __ldcg(&S.beta), __ldcg(&S.halo_seq), cnt, smem_raw, R, acc);
-  if (threadIdx.x == 0) ps->nA = R.n;
-  return acc;
-}
-
-// Phase B with the (new) SpMV input in exchange buffer NB.
-template <int KIND, int NB>
-__device__ __noinline__ double persist_phase_b(volatile PersistState* ps, unsigned long long* bars,
-                                               unsigned char* smem_raw) {
-  const RankDev& P = c_pc.P;
-  const PersistMaps& M = c_pc.M;
-  Scalars& S = P.ctrl->s;
+  __syncwarp();
+  {
+    // beta, the halo version and the stopping decision come from the r.r reduction of the previous iteration
+    // (reduction ps->seq), which the service CTA may still be finishing: phase A starts its loads and waits for
+    // them inside. If the solve turns out to be finished, this phase still runs to its barrier (its output is
+    // never used) so that all CTAs and all ranks leave the loop at the same place.
+    Ring R{smem_u32(bars), smem_u32(bars + kMaxStages), ps->nA};
+    double acc = 0.0;
+    int done_seen = 0;
+    phase_pspmv<KIND>(P, GA, &M.rh, &M.e[CUR], &M.e[NB], &M.rh_h, &M.e_h[CUR], &M.e_h[NB], P.exch[CUR], P.exch[NB], NB,
+                      0.0, 0, cnt, smem_raw, R, acc, true, ps->seq, &done_seen);
+    if (threadIdx.x == 0) ps->nA = R.n;
+    __syncwarp();
+    persist_arrive(P, acc, ps, red_smem, done_seen, false);
+  }
+  if (ps->stop) return false;
   if (threadIdx.x == kNC) asm volatile("fence.proxy.async;" ::: "memory");
-  Ring R{smem_u32(bars + 2 * kMaxStages), smem_u32(bars + 3 * kMaxStages), ps->nB};
-  double acc = 0.0;
-  phase_spmv<KIND, 2>(P, c_pc.GB, &M.e[NB], &M.e_h[NB], &M.x, &M.r, nullptr, __ldcg(&S.alpha), __ldcg(&S.halo_seq), smem_raw,
-                      R, acc);
-  if (threadIdx.x == 0) ps->nB = R.n;
-  return acc;
+  __syncwarp();
+  {
+    Ring R{smem_u32(bars + 2 * kMaxStages), smem_u32(bars + 3 * kMaxStages), ps->nB};
+    double acc = 0.0;
+    phase_spmv<KIND, 2>(P, GB, &M.e[NB], &M.e_h[NB], &M.x, &M.r, nullptr, 0.0, __ldcg(&P.ctrl->s.halo_seq), smem_raw, R,
+                        acc, true, ps->seq);
+    if (threadIdx.x == 0) ps->nB = R.n;
+    __syncwarp();
+    persist_arrive(P, acc, ps, red_smem, 0, true);
+  }
+  return true;
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(kNT, 1) k_cg_persist(int cur0, int niter) {
+__global__ void __launch_bounds__(kNT, 1) k_cg_persist(const __grid_constant__ RankDev P,
+                                                        const PersistMaps* __restrict__ Mp,
+                                                        const __grid_constant__ BandGeo GA,
+                                                        const __grid_constant__ BandGeo GB, int cur0, int niter) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ double red_smem[64];
   __shared__ __align__(8) unsigned long long bars[4 * kMaxStages];
   __shared__ unsigned cnt[CGB_NDIR];
   __shared__ PersistState ps_mem;
   volatile PersistState* ps = &ps_mem;
-  Scalars& S = c_pc.P.ctrl->s;
-  Ring RA, RB;
-  ring_init(RA, bars, c_pc.GA.nstages);
-  ring_init(RB, bars + 2 * kMaxStages, c_pc.GB.nstages);
-  if (threadIdx.x == 0) {
-    // Every CTA reads the barrier generation before it can possibly move: it only advances once ALL CTAs of
-    // this launch have arrived at the first barrier.
-    ps->seq = __ldcg(&S.gbar);
+  Scalars& S = P.ctrl->s;
+  if (blockIdx.x == gridDim.x - 1) {  // the service CTA: one warp, everything else leaves
+    if (threadIdx.x < 32) persist_service(P, niter);
+    return;
+  }
+  // Nothing below diverges inside a warp before the first barrier: all threads run the same straight-line code
+  // (predicated mbarrier inits, every thread stores the same initial loop state). With a one-thread block here,
+  // ptxas emitted no reconvergence point for it (the function is full of early exits), lanes 1-31 of warp 0 ran
+  // ahead of thread 0 and clobbered the uniform registers its stores still needed: the loop state never reached
+  // shared memory and the kernel dead-locked (found on B200, only for some code layouts).
+  ring_init_uniform(bars, GA.nstages);
+  ring_init_uniform(bars + 2 * kMaxStages, GB.nstages);
+  {
+    // Every CTA reads the barrier generation before it can possibly move: it only advances once ALL working CTAs
+    // of this launch have arrived at the first barrier. At entry sbar == gbar (the previous launch has completed).
+    const u64 g0 = __ldcg(&S.gbar);
+    const int stop0 = __ldcg(&S.done) != 0 ? 1 : 0;
+    ps->seq = g0;       // (all threads store identical values)
     ps->nA = 0u;
     ps->nB = 0u;
     ps->it = 0;
-    ps->stop = __ldcg(&S.done) != 0 ? 1 : 0;
+    ps->stop = stop0;
   }
-  __syncthreads();
+  block_sync();
+  // `cur` selects one of two instantiations per iteration; the loop is kept reducible (no jump into its middle for
+  // an odd entry parity), which ptxas needs to place its reconvergence points.
   int cur = cur0;
 #pragma unroll 1
-  while (!ps->stop && ps->it < niter) {
-    if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
-    __syncthreads();
-    double acc = cur == 0 ? persist_phase_a<KIND, 0>(ps, bars, cnt, smem_raw) : persist_phase_a<KIND, 1>(ps, bars, cnt, smem_raw);
-    persist_barrier(acc, ps, red_smem, 0);
-    if (ps->stop) break;
-    acc = cur == 0 ? persist_phase_b<KIND, 1>(ps, bars, smem_raw) : persist_phase_b<KIND, 0>(ps, bars, smem_raw);
-    persist_barrier(acc, ps, red_smem, 1);
+  for (;;) {
+    const bool go = cur == 0 ? persist_iteration<KIND, 0>(P, *Mp, GA, GB, niter, ps, bars, cnt, red_smem, smem_raw)
+                             : persist_iteration<KIND, 1>(P, *Mp, GA, GB, niter, ps, bars, cnt, red_smem, smem_raw);
+    if (!go) break;
     cur ^= 1;
   }
 }
@@ -1072,85 +1298,65 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const map
   return cudaGetLastError();
 }
 
-namespace {
-constexpr int kSlots = 8;
-struct PersistDevice {
-  bool ready = false;
-  cudaEvent_t last_use = nullptr;       // completion of the newest launch that reads c_pc on this device
-  PersistConst* stage = nullptr;        // pinned ring: source of the asynchronous constant refresh
-  cudaEvent_t copied[kSlots] = {};      // the refresh that read slot i has executed
-  unsigned next = 0;
-};
-std::mutex g_persist_mu;
-PersistDevice g_persist_dev[64];
-}  // namespace
-
-// Per-device one-time set-up of the persistent kernel (function attributes, events, pinned staging ring).
-// It allocates, so it belongs to cgb_solve_prepare, not to the launch path. The caller has made `device` current.
+// Per-device one-time set-up of the persistent kernel. The caller has made `device` current.
 cudaError_t cg_persist_prepare(int device) {
+  static std::mutex mu;
+  static bool attr_set[64] = {};
   if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
-  std::lock_guard<std::mutex> lock(g_persist_mu);
-  PersistDevice& D = g_persist_dev[device];
-  if (D.ready) return cudaSuccess;
+  std::lock_guard<std::mutex> lock(mu);
+  if (attr_set[device]) return cudaSuccess;
   const auto at = cudaFuncAttributeMaxDynamicSharedMemorySize;
   cudaError_t e = cudaFuncSetAttribute(k_cg_persist<CGB_KIND_POISSON3D7>, at, 220 * 1024);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_cg_persist<CGB_KIND_STENCIL3D27>, at, 220 * 1024);
   if (e == cudaSuccess) e = cudaFuncSetAttribute(k_cg_persist<CGB_KIND_POISSON2D5>, at, 220 * 1024);
-  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&D.last_use, cudaEventDisableTiming);
-  for (int k = 0; k < kSlots && e == cudaSuccess; ++k) e = cudaEventCreateWithFlags(&D.copied[k], cudaEventDisableTiming);
-  if (e == cudaSuccess) e = cudaMallocHost(&D.stage, kSlots * sizeof(PersistConst));
   if (e != cudaSuccess) return e;
-  D.ready = true;
+  attr_set[device] = true;
   return cudaSuccess;
 }
 
-// maps: r (with halo rows), exch[0], exch[1], their three 2-column halo-box twins, then x and r (band rows).
-// The caller has made `device` current and has called cg_persist_prepare(device).
-cudaError_t launch_cg_persist(const RankDev& P, int device, const void* const maps[8], int cur, int niter,
-                              cudaStream_t s) {
-  if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
-  std::lock_guard<std::mutex> lock(g_persist_mu);
-  PersistDevice& D = g_persist_dev[device];
-  if (!D.ready) return cudaErrorNotReady;
-  int nsm = 148;
-  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device);
-  const unsigned slot = D.next++ % kSlots;
-  cudaError_t e = cudaEventSynchronize(D.copied[slot]);  // returns at once unless 8 refreshes are still queued
-  if (e != cudaSuccess) return e;
-  PersistConst& pc = D.stage[slot];
-  int ga, gb;
-  size_t sa, sb;
-  if (!make_geo(P, nsm, kSpmvPUpdate, &pc.GA, &ga, &sa) || !make_geo(P, nsm, kSpmvUpdate, &pc.GB, &gb, &sb))
-    return cudaErrorInvalidConfiguration;
+size_t cg_persist_maps_bytes() { return sizeof(PersistMaps); }
+
+// Copy the eight host-built tensor maps (order: r with halo rows, exch[0], exch[1], their three 2-column halo-box
+// twins, x, r band rows) into the context's device-resident PersistMaps block.
+cudaError_t cg_persist_upload_maps(void* d_maps, const void* const maps[8]) {
+  PersistMaps M;
   for (int k = 0; k < 8; ++k)
     if (!maps[k]) return cudaErrorInvalidValue;
-  pc.P = P;
-  pc.M.rh = *reinterpret_cast<const CUtensorMap*>(maps[0]);
-  pc.M.e[0] = *reinterpret_cast<const CUtensorMap*>(maps[1]);
-  pc.M.e[1] = *reinterpret_cast<const CUtensorMap*>(maps[2]);
-  pc.M.rh_h = *reinterpret_cast<const CUtensorMap*>(maps[3]);
-  pc.M.e_h[0] = *reinterpret_cast<const CUtensorMap*>(maps[4]);
-  pc.M.e_h[1] = *reinterpret_cast<const CUtensorMap*>(maps[5]);
-  pc.M.x = *reinterpret_cast<const CUtensorMap*>(maps[6]);
-  pc.M.r = *reinterpret_cast<const CUtensorMap*>(maps[7]);
-  const int grid = ga > gb ? ga : gb;    // one CTA per SM (make_geo caps both at the SM count): all co-resident
+  M.rh = *reinterpret_cast<const CUtensorMap*>(maps[0]);
+  M.e[0] = *reinterpret_cast<const CUtensorMap*>(maps[1]);
+  M.e[1] = *reinterpret_cast<const CUtensorMap*>(maps[2]);
+  M.rh_h = *reinterpret_cast<const CUtensorMap*>(maps[3]);
+  M.e_h[0] = *reinterpret_cast<const CUtensorMap*>(maps[4]);
+  M.e_h[1] = *reinterpret_cast<const CUtensorMap*>(maps[5]);
+  M.x = *reinterpret_cast<const CUtensorMap*>(maps[6]);
+  M.r = *reinterpret_cast<const CUtensorMap*>(maps[7]);
+  return cudaMemcpy(d_maps, &M, sizeof(M), cudaMemcpyHostToDevice);
+}
+
+// d_maps: the context's device-resident PersistMaps (cg_persist_upload_maps). The caller has made `device`
+// current and has called cg_persist_prepare(device).
+cudaError_t launch_cg_persist(const RankDev& P, int device, const void* d_maps, int cur, int niter, cudaStream_t s) {
+  int nsm = 148;
+  cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, device);
+  BandGeo GA, GB;
+  int ga, gb;
+  size_t sa, sb;
+  // one SM is reserved for the service CTA (cross-GPU reductions off the critical path)
+  if (!make_geo(P, nsm - 1, kSpmvPUpdate, &GA, &ga, &sa) || !make_geo(P, nsm - 1, kSpmvUpdate, &GB, &gb, &sb))
+    return cudaErrorInvalidConfiguration;
+  if (!d_maps) return cudaErrorInvalidValue;
+  const int grid = (ga > gb ? ga : gb) + 1;  // working CTAs + the service CTA, one per SM: all co-resident
   const size_t sm = sa > sb ? sa : sb;
+  RankDev Pc = P;
+  const void* Mp = d_maps;
+  void* args[] = {&Pc, &Mp, &GA, &GB, &cur, &niter};
   const void* fn = P.st.kind == CGB_KIND_POISSON3D7    ? (const void*)k_cg_persist<CGB_KIND_POISSON3D7>
                    : P.st.kind == CGB_KIND_STENCIL3D27 ? (const void*)k_cg_persist<CGB_KIND_STENCIL3D27>
                    : P.st.kind == CGB_KIND_POISSON2D5  ? (const void*)k_cg_persist<CGB_KIND_POISSON2D5>
                                                        : nullptr;
   if (!fn) return cudaErrorInvalidValue;
-  // c_pc is shared by every context on this device: the refresh waits (on the device, not on the host) for the
-  // previous launch that read it, whichever stream or context that was on.
-  e = cudaStreamWaitEvent(s, D.last_use, 0);
-  if (e == cudaSuccess) e = cudaMemcpyToSymbolAsync(c_pc, &pc, sizeof(pc), 0, cudaMemcpyHostToDevice, s);
-  if (e == cudaSuccess) e = cudaEventRecord(D.copied[slot], s);
-  if (e != cudaSuccess) return e;
-  void* args[] = {&cur, &niter};
   // cooperative: the launch fails instead of dead-locking if the CTAs cannot all be resident at once
-  e = cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kNT), args, sm, s);
-  if (e == cudaSuccess) e = cudaEventRecord(D.last_use, s);
-  return e;
+  return cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(kNT), args, sm, s);
 }
 
 bool cg_persist_supported(int device) {

@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <climits>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 
@@ -71,6 +72,7 @@ int alloc_common(cgb_ctx* c) {
   P.hist_cap = c->hist_cap;
   P.nranks = c->part.nranks;
   P.rank = c->part.rank;
+  if (const char* e = std::getenv("CGB_DEBUG_FLAGS")) P.dbg_flags = std::atoi(e);
   P.lay = c->lay;
   P.st = c->st;
   P.y0 = c->part.y0;
@@ -90,6 +92,11 @@ int alloc_common(cgb_ctx* c) {
     int r6 = spmv_tma_make_map(c->st.kind, c->lay, P.exch[1], c->tmap_h[1], 1, 2);
     int r7 = spmv_tma_make_map(c->st.kind, c->lay, P.r, c->tmap_rh_h, 1, 2);
     c->tma_ok = (r0 | r1 | r2 | r3 | r4 | r5 | r6 | r7) == CGB_OK;
+    if (c->tma_ok) {  // the persistent kernel reads its descriptors from device memory
+      CGB_CUDA(cudaMalloc(&c->d_maps, cg_persist_maps_bytes()));
+      const void* maps[8] = {c->tmap_rh, c->tmap[0], c->tmap[1], c->tmap_rh_h, c->tmap_h[0], c->tmap_h[1], c->tmap_x, c->tmap_r};
+      CGB_CUDA(cg_persist_upload_maps(c->d_maps, maps));
+    }
   }
   // timeout for peer waits lives in the control block and survives solves
   Scalars init{};
@@ -109,6 +116,7 @@ cgb_ctx::~cgb_ctx() {
   if (arena) cudaFree(arena);
   if (local) cudaFree(local);
   if (extra) cudaFree(extra);
+  if (d_maps) cudaFree(d_maps);
   if (compact_tmp) cudaFree(compact_tmp);
   if (d_rowptr) cudaFree(d_rowptr);
   if (d_colind) cudaFree(d_colind);
@@ -472,6 +480,22 @@ extern "C" int cgb_ctx_set_trace(cgb_ctx* c, unsigned long long* dev_buf, int ca
   return CGB_OK;
 }
 
+// Device-resident solver state to stderr (post-mortem of a CGB_ERR_TIMEOUT; synchronises the device).
+extern "C" int cgb_ctx_debug_print(cgb_ctx* c) {
+  CGB_REQUIRE(c, "cgb_ctx_debug_print: NULL context");
+  CGB_CUDA(cudaSetDevice(c->device));
+  Scalars s;
+  CGB_CUDA(cudaMemcpy(&s, &c->P.ctrl->s, sizeof(Scalars), cudaMemcpyDeviceToHost));
+  std::fprintf(stderr,
+               "[cgb rank %d] iter=%d done=%d maxit=%d rho=%.6e alpha=%.6e beta=%.6e rnorm=%.6e red_seq=%llu halo_seq=%llu "
+               "gbar=%llu sbar=%llu ticket=%u dbg={site=%d block=%d thread=%d %d %d %d %d %d | %08x %08x %08x %08x %08x %08x}\n",
+               c->part.rank, s.iter, s.done, s.maxit, s.rho, s.alpha, s.beta, s.rnorm, s.red_seq, s.halo_seq, s.gbar, s.sbar,
+               s.ticket_red, s.dbg[0], s.dbg[1], s.dbg[2], s.dbg[3], s.dbg[4], s.dbg[5], s.dbg[6], s.dbg[7], s.dbg[8], s.dbg[9], s.dbg[10],
+               s.dbg[11], s.dbg[12], s.dbg[13]);
+  std::fprintf(stderr, "[cgb rank %d] dbg[12..15] = %d %d %d %d\n", c->part.rank, s.dbg[12], s.dbg[13], s.dbg[14], s.dbg[15]);
+  return CGB_OK;
+}
+
 extern "C" int64_t cgb_ctx_launch_count(cgb_ctx* c) { return c ? c->launches : 0; }
 
 // ---------------------------------------------------------------------------------------------
@@ -526,8 +550,7 @@ static int enqueue_spmv(cgb_ctx* c, int buf, int mode, cudaStream_t s) {
 
 // `n` iterations of the merged variant in ONE cooperative launch (grid barrier + all-reduce on the device).
 static int enqueue_persist(cgb_ctx* c, int n, cudaStream_t s) {
-  const void* maps[8] = {c->tmap_rh, c->tmap[0], c->tmap[1], c->tmap_rh_h, c->tmap_h[0], c->tmap_h[1], c->tmap_x, c->tmap_r};
-  CGB_CUDA(launch_cg_persist(c->P, c->device, maps, c->host_cur, n, s));
+  CGB_CUDA(launch_cg_persist(c->P, c->device, c->d_maps, c->host_cur, n, s));
   c->host_cur ^= (n & 1);
   return CGB_OK;
 }

@@ -60,6 +60,7 @@ struct cgb_ctx {
   alignas(64) unsigned char tmap_rh[128] = {};  // r with halo rows (merged variant)
   alignas(64) unsigned char tmap_h[2][128] = {};  // 2-column x-halo boxes of exch[0], exch[1] (tiled rows)
   alignas(64) unsigned char tmap_rh_h[128] = {};  // ... and of r
+  void* d_maps = nullptr;  // the same eight maps in device memory: descriptor source of the persistent kernel
   bool tma_ok = false;
 
   ~cgb_ctx();

@@ -114,6 +114,7 @@ def _declare(lib):
         "cgb_solve_poll": (C.c_int, [vp, C.c_int, P(SolveResult)]),
         "cgb_solve_finish": (C.c_int, [vp, P(SolveResult)]),
         "cgb_ctx_set_trace": (C.c_int, [vp, vp, C.c_int]),
+        "cgb_ctx_debug_print": (C.c_int, [vp]),
         "cgb_ctx_launch_count": (i64, [vp]),
         "cgb_op_scratch_bytes": (C.c_size_t, []),
         "cgb_op_dot": (C.c_int, [vp, vp, i64, vp, vp, vp]),

@@ -264,6 +264,9 @@ int cgb_solve_finish(cgb_ctx* c, cgb_solve_result_t* res);
  * reached the p.Ap barrier, alpha released, last CTA reached the r.r barrier, beta released - which splits an
  * iteration into compute and rendezvous time. dev_buf: device memory for 4*cap_iters u64, or NULL to switch off. */
 int cgb_ctx_set_trace(cgb_ctx* c, unsigned long long* dev_buf, int cap_iters);
+/* Print the device-resident solver state (iteration, scalars, barrier generations, the site of a timed-out wait)
+ * to stderr: post-mortem aid after CGB_ERR_TIMEOUT. Synchronises the device. */
+int cgb_ctx_debug_print(cgb_ctx* c);
 /* Kernels launched by this context so far (what bench.py reports as gpu_launches). */
 int64_t cgb_ctx_launch_count(cgb_ctx* c);
 
