@@ -91,8 +91,10 @@ extern "C" const char* cgb_refstyle_last_error(void) { return g_err.c_str(); }
 // Runs `warmup` untimed + `steps` timed iterations of the reference loop (no early exit: the
 // residual test is evaluated like the reference does, but tol is 0). Returns ms for the timed
 // iterations (CUDA events on the default stream) and the last ||r||.
-extern "C" int cgb_refstyle_run(int kind, int gx, int gy, int gz, int faithful, int warmup, int steps, double* out_ms,
-                                double* out_rnorm, long long* out_nnz) {
+// b_dev (may be NULL: built-in hash RHS): n doubles on the device. hist (may be NULL): host array that receives
+// ||r||_2 after each of the warmup+steps iterations, so that the baseline's numerics can be pinned to the solver's.
+extern "C" int cgb_refstyle_run2(int kind, int gx, int gy, int gz, int faithful, int warmup, int steps,
+                                 const double* b_dev, double* hist, double* out_ms, double* out_rnorm, long long* out_nnz) {
   Grid g{kind, gx, gy, gz, 0, -1.0, -1.0, -1.0};
   g.cc = kind == 1 ? 4.0 : (kind == 2 ? 6.0 : 26.0);
   const long long n = (long long)gx * gy * gz;
@@ -120,7 +122,8 @@ extern "C" int cgb_refstyle_run(int kind, int gx, int gy, int gz, int faithful, 
   k_assemble<<<1184, 256>>>(g, n, rowptr, colind, val, 1);
   RS_CUDA(cudaGetLastError());
   for (double** v : {&b, &x, &r, &p, &Ap}) RS_CUDA(cudaMalloc(v, (size_t)n * sizeof(double)));
-  k_fill_rhs<<<1184, 256>>>(b, n, 1);
+  if (b_dev) RS_CUDA(cudaMemcpy(b, b_dev, (size_t)n * sizeof(double), cudaMemcpyDeviceToDevice));
+  else k_fill_rhs<<<1184, 256>>>(b, n, 1);
   RS_CUDA(cudaMemset(x, 0, (size_t)n * sizeof(double)));  // the reference forgets this (CUDACG.cu:182-186)
 
   cublasHandle_t hb;
@@ -170,6 +173,7 @@ extern "C" int cgb_refstyle_run(int kind, int gx, int gy, int gz, int faithful, 
     rhop = rho;
     RS_LIB(cublasDnrm2(hb, nn, r, 1, &rho), CUBLAS_STATUS_SUCCESS);
     *out_rnorm = rho;
+    if (hist) hist[it] = rho;
     rho = rho * rho;
     beta = rho / rhop;
     RS_LIB(cublasDscal(hb, nn, &beta, p, 1), CUBLAS_STATUS_SUCCESS);
@@ -191,4 +195,9 @@ extern "C" int cgb_refstyle_run(int kind, int gx, int gy, int gz, int faithful, 
   for (void* v : {(void*)rowptr, (void*)colind, (void*)val, (void*)b, (void*)x, (void*)r, (void*)p, (void*)Ap, dBuffer})
     if (v) cudaFree(v);
   return 0;
+}
+
+extern "C" int cgb_refstyle_run(int kind, int gx, int gy, int gz, int faithful, int warmup, int steps, double* out_ms,
+                                double* out_rnorm, long long* out_nnz) {
+  return cgb_refstyle_run2(kind, gx, gy, gz, faithful, warmup, steps, nullptr, nullptr, out_ms, out_rnorm, out_nnz);
 }

@@ -38,7 +38,9 @@ def parse():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "refstyle"])
-    ap.add_argument("--problem", default="poisson3d7", choices=["poisson2d5", "poisson3d7", "stencil3d27"])
+    ap.add_argument("--problem", default="poisson3d7", choices=["poisson2d5", "poisson3d7", "stencil3d27", "csr7"],
+                    help="csr7 = the 7-point operator ASSEMBLED as a general CSR matrix (the reference's own capability, "
+                         "CUDACG.cu:213-216,288-291): like-for-like against --impl refstyle on the same matrix")
     ap.add_argument("--grid", type=int, nargs="+", default=None, help="grid extents (default: the headline 512^3)")
     ap.add_argument("--variant", default=os.environ.get("CGB_VARIANT", "auto"))
     ap.add_argument("--spmv", default=os.environ.get("CGB_SPMV", "auto"))
@@ -60,14 +62,19 @@ def main():
                           "reference is one main() hard-wired to a 3x3 system (CUDACG.cu:83-117): no problem-size "
                           "input, no setup.py/pyproject, cannot run the 512^3 configuration; see --impl refstyle"}))
         return 0
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if a.impl == "refstyle":
+        # our restatement of the reference's library-call sequence (B3 on one GPU, B4 = + NCCL + peer copies on N);
+        # at N > 1 rank 0 drives all GPUs from one process, so no torch process group is set up here
+        from baseline import refstyle
+        return refstyle.bench(a, rank, local_rank, world)
     import torch
     import torch.distributed as dist
     from cuda_mpi_parallel_b200 import CGSolver, Problem
     from cuda_mpi_parallel_b200.parallel import attach_torch_distributed
 
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
     if world != a.gpus:
         if world == 1 and a.gpus > 1:
             raise SystemExit("launch with torch.distributed.run --nproc-per-node N for --gpus N > 1")
@@ -76,15 +83,20 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    if a.impl == "refstyle":
-        from baseline import refstyle
-        return refstyle.bench(a, rank, local_rank, world)
-
-    defaults = {"poisson3d7": [512, 512, 512], "poisson2d5": [8192, 8192], "stencil3d27": [384, 384, 384]}
+    defaults = {"poisson3d7": [512, 512, 512], "poisson2d5": [8192, 8192], "stencil3d27": [384, 384, 384],
+                "csr7": [512, 512, 512]}
     grid = a.grid or defaults[a.problem]
     if len(grid) == 1:
         grid = grid * (2 if a.problem == "poisson2d5" else 3)
-    prob = Problem.from_name(a.problem, grid)
+    if a.problem == "csr7":
+        if world != 1:
+            raise SystemExit("--problem csr7 is the single-GPU like-for-like race against the reference-style baseline")
+        stencil_prob = Problem.from_name("poisson3d7", grid)
+        rowptr, colind, val = stencil_prob.to_csr()          # assembled on the host, copied H2D like CUDACG.cu:120-134
+        prob = Problem.csr(rowptr, colind, val, name="csr7")
+        del rowptr, colind, val
+    else:
+        prob = Problem.from_name(a.problem, grid)
     K, W = a.steps, max(a.warmup, 3)
     chunk = a.chunk or max(1, min(25, K))   # graphs are captured and uploaded in begin(), not in the timed region
     stream = torch.cuda.Stream()
@@ -106,7 +118,12 @@ def main():
     if trace is not None:
         solver.set_trace(trace)
     with torch.cuda.stream(stream):
-        solver.set_rhs("random", seed=1)
+        if a.problem == "csr7":      # same hash-random RHS as the stencil runs and as the refstyle baseline
+            b_dev = torch.from_numpy(stencil_prob.rhs("random", seed=1)).cuda()
+            stream.wait_stream(torch.cuda.default_stream())
+            solver.set_rhs(b_dev, stream=stream)
+        else:
+            solver.set_rhs("random", seed=1)
         solver.begin(fixed_iters=W + K, variant=a.variant, spmv=a.spmv, chunk=chunk, stream=stream, persistent=persistent)
         solver.iterate(W)
         barrier()
@@ -148,7 +165,10 @@ def main():
         # the same hash-random RHS as the kernel arm, generated from the GLOBAL index: the residuals below do not
         # depend on how many ranks share the grid
         b_host = torch.empty(solver.n_local, dtype=torch.float64).pin_memory()
-        prob.rhs_local(solver.part, "random", seed=1, out=b_host)
+        if a.problem == "csr7":
+            b_host.copy_(torch.from_numpy(stencil_prob.rhs("random", seed=1)))
+        else:
+            prob.rhs_local(solver.part, "random", seed=1, out=b_host)
         hist = torch.zeros(K, dtype=torch.float64).pin_memory()
         solver.set_host_history(hist)          # every step's ||r||_2 lands in pinned host memory (8-byte D2H per step)
         with torch.cuda.stream(stream):
@@ -184,7 +204,7 @@ def main():
             if a.problem == "poisson3d7" and grid == [512, 512, 512] else f"CG iterations/s ({a.problem} {grid})",
             "value": its, "unit": "CG iterations/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": ms / K, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "fp64", "data": "synthetic (hash-random RHS, matrix-free Poisson operator)",
+            "dtype": "fp64", "data": "synthetic (hash-random RHS, " + ("assembled CSR 7-point operator)" if a.problem == "csr7" else "matrix-free Poisson operator)"),
             "gdof_per_s": its * n / 1e9,
             "config": {"model": f"{a.problem} {'x'.join(map(str, grid))} fp64 unpreconditioned CG",
                        "global_batch": n, "seq_len": None,

@@ -323,6 +323,76 @@ __global__ void __launch_bounds__(kThreads) k_spmv_csr(const __grid_constant__ R
 }
 
 // ---------------------------------------------------------------------------------------------
+// k_spmv_csr_stream: general CSR for matrices with short rows (what cusparseSpMV does at CUDACG.cu:288-291).
+// The host cuts the rows into blocks of <= kThreads rows and <= kCsrCap nonzeros. A CTA streams the block's
+// val/colind - one contiguous range of the CSR arrays - with 128-bit / 64-bit loads, all of them independent
+// (two entries per thread per step), multiplies by the gathered x and parks the products in shared memory;
+// then one thread per row adds its products in order (deterministic). A row longer than kCsrCap forms a block
+// of its own and is reduced by the whole CTA. DRAM traffic: 12 B per nonzero + 4 B of row offsets + y, with x
+// mostly served by L2; there is no per-row shuffle tree and no dependent rowptr -> colind -> x chain per lane.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_spmv_csr_stream(const __grid_constant__ RankDev P,
+                                                               const double* __restrict__ in, double* __restrict__ out,
+                                                               int mode) {
+  __shared__ double prod[kCsrCap];
+  __shared__ double red_smem[64];
+  Scalars& S = P.ctrl->s;
+  if (S.done != 0) return;
+  const int* __restrict__ rowptr = P.csr_rowptr;
+  const int* __restrict__ col = P.csr_colind;
+  const double* __restrict__ val = P.csr_val;
+  const int* __restrict__ rowblk = P.csr_rowblk;
+  double acc = 0.0;
+  for (int b = blockIdx.x; b < P.csr_nblk; b += gridDim.x) {
+    const int r0 = rowblk[b], r1 = rowblk[b + 1];
+    const int e0 = rowptr[r0], e1 = rowptr[r1];
+    if (e1 - e0 <= kCsrCap) {
+      const int ea = e0 & ~1;  // pairs start at even entries: val pairs are 16-byte, colind pairs 8-byte aligned
+      for (int e = ea + 2 * (int)threadIdx.x; e < e1; e += 2 * kThreads) {
+        if (e >= e0 && e + 1 < e1) {
+          const double2 v = ld2(val + e);
+          const int2 c = *reinterpret_cast<const int2*>(col + e);
+          prod[e - e0] = v.x * in[c.x];
+          prod[e + 1 - e0] = v.y * in[c.y];
+        } else {
+          if (e >= e0) prod[e - e0] = val[e] * in[col[e]];
+          if (e + 1 < e1) prod[e + 1 - e0] = val[e + 1] * in[col[e + 1]];
+        }
+      }
+      block_sync();
+      const int r = r0 + (int)threadIdx.x;
+      if (r < r1) {
+        const int a = rowptr[r] - e0, z = rowptr[r + 1] - e0;
+        double s = 0.0;
+        for (int k = a; k < z; ++k) s += prod[k];
+        out[r] = s;
+        acc += in[r] * s;
+      }
+      block_sync();  // prod is reused by the next block
+    } else {
+      // a single long row: every thread strides over it, fixed-order tree over the CTA
+      double s = 0.0, z = 0.0;
+      for (int e = e0 + (int)threadIdx.x; e < e1; e += kThreads) s += val[e] * in[col[e]];
+      block_sum2(s, z, red_smem);
+      if (threadIdx.x == 0) {
+        out[r0] = s;
+        acc += in[r0] * s;
+      }
+      block_sync();
+    }
+  }
+  if (mode == kSpmvPlain) return;
+  double a = acc, z = 0.0;
+  if (grid_sum2_last(a, z, P.partials, &S.ticket_red, red_smem)) {
+    allreduce2_last_cta(P, a, z, red_smem);
+    if (threadIdx.x == 0 && mode == kSpmvAlpha) {
+      S.pAp = a;
+      S.alpha = S.rho / a;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // k_update: x += alpha p ; r -= alpha Ap ; rho' = r.r ; then, on the last CTA, the reference's
 // stopping test (absolute ||r||_2 < tol, after the x/r update and before the p update,
 // CUDACG.cu:333) and beta (CUDACG.cu:339).
@@ -528,7 +598,23 @@ int query_launch_cfg(int device, LaunchCfg* cfg) {
   int g = occ_grid(k_spmv<CGB_KIND_STENCIL3D27>, device, kMaxGrid);
   cfg->grid_spmv = g;
   cfg->grid_csr = occ_grid(k_spmv_csr<8>, device, kMaxGrid);
+  cfg->grid_csr_stream = occ_grid(k_spmv_csr_stream, device, kMaxGrid);
   return 0;
+}
+
+std::vector<int> csr_row_blocks(int n, const int* rowptr) {
+  std::vector<int> blk;
+  blk.reserve((size_t)n / 128 + 2);
+  blk.push_back(0);
+  int r = 0;
+  while (r < n) {
+    const int e0 = rowptr[r];
+    int r1 = r + 1;  // a block always takes at least one row, however long
+    while (r1 < n && r1 - r < kThreads && rowptr[r1 + 1] - e0 <= kCsrCap) ++r1;
+    blk.push_back(r1);
+    r = r1;
+  }
+  return blk;
 }
 
 void choose_spmv_tiling(RankDev& P, int grid_spmv) {
@@ -577,6 +663,11 @@ cudaError_t launch_spmv_simple(const RankDev& P, const LaunchCfg& c, const doubl
 
 cudaError_t launch_spmv_csr(const RankDev& P, const LaunchCfg& c, const double* in, double* out, int mode,
                             cudaStream_t s) {
+  if (P.csr_rowblk && P.csr_nblk > 0 && !P.csr_dist) {  // row blocks were built: the streaming kernel
+    int grid = P.csr_nblk < c.grid_csr_stream ? P.csr_nblk : c.grid_csr_stream;
+    k_spmv_csr_stream<<<grid, kThreads, 0, s>>>(P, in, out, mode);
+    return cudaGetLastError();
+  }
   const int n = P.lay.nx;
   // lanes per row ~ average nonzeros per row, rounded to a power of two
   const long long nnz_avg = P.csr_avg_nnz;

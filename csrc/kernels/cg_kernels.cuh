@@ -1,5 +1,7 @@
 // Launch wrappers of the CG kernels (definitions in cg_kernels.cu, spmv_tma.cu, pipecg_kernels.cu).
 #pragma once
+#include <vector>
+
 #include "dev_common.cuh"
 
 namespace cgb {
@@ -18,7 +20,13 @@ struct LaunchCfg {
   int grid_ew;    // persistent grid of the elementwise kernels
   int grid_spmv;  // persistent grid of the simple stencil SpMV
   int grid_csr;
+  int grid_csr_stream;
 };
+
+constexpr int kCsrCap = 2048;  // nonzeros per row block of k_spmv_csr_stream (16 KB of products in shared memory)
+// Cut rows [0,n) into blocks of <= 256 rows and <= kCsrCap nonzeros (a longer row gets a block of its own).
+// Host only; returns the block boundaries (nblk+1 entries).
+std::vector<int> csr_row_blocks(int n, const int* rowptr);
 
 // Occupancy-derived persistent grid sizes for this device.
 int query_launch_cfg(int device, LaunchCfg* cfg);

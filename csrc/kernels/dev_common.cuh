@@ -50,7 +50,7 @@ struct Scalars {
   int cur;           // pipelined CG: exchange buffer that holds the current w (diagnostic)
   unsigned int ticket_red;
   unsigned int ticket_halo[CGB_NDIR];
-  int dbg[16];       // post-mortem of a timed-out wait: site code, block, thread, ... (cgb_ctx_debug_print)
+  int dbg[8];        // post-mortem of a timed-out wait: site code, block, thread, ... (cgb_ctx_debug_print)
 };
 
 // Peers write red_ll and halo_flag with P2P stores; everything from `s` on is rank-local.
@@ -97,6 +97,8 @@ struct RankDev {
   const int* csr_colind;
   const double* csr_val;
   int csr_avg_nnz;   // ceil(nnz/n): picks the lanes-per-row of k_spmv_csr
+  const int* csr_rowblk;  // row blocks of the streaming CSR kernel: block b = rows [rowblk[b], rowblk[b+1]); NULL: none
+  int csr_nblk;
   // row-block distributed CSR: remote entries of p are loaded from the owners' exchange buffers
   int csr_dist;                          // 1 if the columns span several ranks
   int csr_n_global;

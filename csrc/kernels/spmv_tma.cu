@@ -27,7 +27,9 @@
 // problems and general CSR use the L1-path kernels.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
+#include <utility>
 
 #include "../common/status.hpp"
 #include "cg_kernels.cuh"
@@ -82,13 +84,26 @@ __device__ __forceinline__ void mbar_arrive(unsigned bar) {
 // within the peer-wait timeout (a lost TMA transaction, a dead producer), the solve is failed with
 // CGB_ERR_TIMEOUT and the wait - and every later one, which sees the failed state after its first unsuccessful
 // try - falls through, so the kernel drains instead of hanging. `site` lands in Scalars::dbg for the post-mortem.
-__device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
+// Hot path: one asm block that retries try_wait up to 4096 times and costs no registers beyond its operands
+// (the 27-point loops run at the register limit: a C-level loop with a clock and a counter there cost them 25 %).
+__device__ __forceinline__ bool mbar_spin(unsigned bar, unsigned parity) {
   unsigned ok;
   asm volatile(
       "{\n"
       ".reg .pred p;\n"
+      ".reg .u32 c;\n"
+      "mov.u32 c, 4096;\n"
+      "SPIN_%=:\n"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-      "selp.u32 %0, 1, 0, p;\n"
+      "@p bra HIT_%=;\n"
+      "sub.u32 c, c, 1;\n"
+      "setp.ne.u32 p, c, 0;\n"
+      "@p bra SPIN_%=;\n"
+      "mov.u32 %0, 0;\n"
+      "bra END_%=;\n"
+      "HIT_%=:\n"
+      "mov.u32 %0, 1;\n"
+      "END_%=:\n"
       "}\n"
       : "=r"(ok)
       : "r"(bar), "r"(parity)
@@ -96,11 +111,10 @@ __device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
   return ok != 0;
 }
 __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity, Scalars& S, int site) {
-  if (mbar_try(bar, parity)) return;
+  if (mbar_spin(bar, parity)) return;
+  // cold: the barrier is late by thousands of polls
   const long long t0 = clock64();
-  unsigned spins = 0;
-  while (!mbar_try(bar, parity)) {
-    if ((++spins & 0xffu) != 0) continue;   // look at the clock and the failure flag only now and then
+  do {
     if (*(volatile int*)&S.done == CGB_ERR_TIMEOUT) return;
     if (clock64() - t0 > 4 * S.timeout_cycles) {
       if (atomicCAS(&S.dbg[0], 0, site) == 0) {  // the first wait that gave up tells the story
@@ -110,25 +124,11 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity, Scalars
         S.dbg[4] = (int)parity;
         S.dbg[5] = (int)*(volatile u64*)&S.gbar;
         S.dbg[6] = (int)*(volatile u64*)&S.sbar;
-        // raw state words of this barrier and of its partner array (full <-> empty are 64 bytes apart)
-        unsigned long long w0, w1, w2;
-        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(w0) : "r"(bar));
-        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(w1) : "r"(bar - 64));
-        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(w2) : "r"(bar - 56));
-        S.dbg[8] = (int)w0;  S.dbg[9] = (int)(w0 >> 32);
-        S.dbg[10] = (int)w1; S.dbg[11] = (int)(w1 >> 32);
-        unsigned crank, cn, dsm, tsm;
-        asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(crank));
-        asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(cn));
-        asm volatile("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dsm));
-        asm volatile("mov.u32 %0, %%total_smem_size;" : "=r"(tsm));
-        S.dbg[12] = (int)crank; S.dbg[13] = (int)cn; S.dbg[14] = (int)dsm; S.dbg[15] = (int)tsm;
-        (void)w2;
       }
       S.done = CGB_ERR_TIMEOUT;
       return;
     }
-  }
+  } while (!mbar_spin(bar, parity));
 }
 __device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, int x, int y, int z, unsigned bar) {
   asm volatile(
@@ -388,6 +388,15 @@ __device__ __forceinline__ void wait_scalars(const RankDev& P, u64 seq) {
   __syncwarp();
 }
 
+// Programmatic dependent launch (PDL): a kernel launched with the programmatic-stream-serialization attribute may
+// start as soon as every CTA of its predecessor has executed launch_dependents (or exited); it must then execute
+// pdl_wait() before it touches anything the predecessor wrote. The band kernels trigger at their very first
+// instruction and wait after their private set-up (mbarrier init), so the next kernel of the iteration is already
+// resident - set up and parked in the wait - on every SM the moment its predecessor's last CTA retires: the launch
+// latency and the prologue leave the critical path of the iteration.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // State of one mbarrier ring: smem addresses of the full/empty barrier arrays and the number of slabs this
 // thread's role has issued (producer lane) or consumed (consumer threads) so far. A persistent kernel keeps
 // one Ring per phase alive across iterations; the per-iteration kernels start one at zero.
@@ -573,10 +582,12 @@ __global__ void __launch_bounds__(kNT, 1) k_spmv_tma(const __grid_constant__ Ran
   __shared__ double red_smem[64];
   __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
   Scalars& S = P.ctrl->s;
-  if (S.done != 0) return;
+  pdl_launch_dependents();
   Ring R;
   ring_init(R, bars, G.nstages);
   block_sync();
+  pdl_wait();  // everything below reads what the previous kernel of the stream produced
+  if (S.done != 0) return;
   double acc = 0.0;
   phase_spmv<KIND, OUT>(P, G, &tmap, &tmap_h, &tmx, &tmr, out, S.alpha, S.halo_seq, smem_raw, R, acc);
   if (mode == kSpmvPlain) return;
@@ -635,7 +646,7 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
     const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
     const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
     const unsigned st = nn % kStages, ph = (nn / kStages) & 1u;
-    mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 1000 + (int)nn);
+    mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 3);
     mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
     const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
     for (int b = 0; b < G.NBX; ++b) {
@@ -770,7 +781,7 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
         const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
         const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
         const bool inb = q >= 0 && q < L.nz;
-        mbar_wait(full0 + 8 * st, ph, S, 2000 + (int)n);
+        mbar_wait(full0 + 8 * st, ph, S, 4);
         const unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
         double2 pna = make_double2(0, 0), pnb = pna;
         PS2 na{}, nb{};
@@ -821,11 +832,13 @@ __global__ void __launch_bounds__(kNT, 1) k_pspmv_tma(const __grid_constant__ Ra
   __shared__ __align__(8) unsigned long long bars[2 * kMaxStages];
   __shared__ unsigned cnt[CGB_NDIR];
   Scalars& S = P.ctrl->s;
-  if (S.done != 0) return;
+  pdl_launch_dependents();
   Ring R;
   ring_init(R, bars, G.nstages);
   if (threadIdx.x < CGB_NDIR) cnt[threadIdx.x] = 0u;
   block_sync();
+  pdl_wait();  // everything below reads what the previous kernel of the stream produced
+  if (S.done != 0) return;
   double acc = 0.0;
   phase_pspmv<KIND>(P, G, &tm_r, &tm_pold, &tm_pnew, &tm_r_h, &tm_pold_h, &tm_pnew_h, pold, pnew, newbuf, S.beta,
                     S.halo_seq, cnt, smem_raw, R, acc);
@@ -933,6 +946,14 @@ __device__ __forceinline__ void persist_service(const RankDev& P, int niter) {
   u64 seq = __ldcg(&S.sbar);
   bool done = __ldcg(&S.done) != 0;
   if (done) return;  // the working CTAs leave at once, too
+  // This warp is the only writer of the CG scalars while the kernel runs, so it keeps them in registers: between
+  // "all partials are in" and "alpha/beta published" there is no dependent load from memory left.
+  double rho = S.rho;
+  const double thresh = S.thresh;
+  const int maxit = S.maxit;
+  int iter = S.iter;
+  u64 halo_seq = S.halo_seq, red_seq = S.red_seq;
+  const long long timeout = S.timeout_cycles;
   for (int it = 0; it < niter; ++it) {
     for (int phase = 0; phase < 2; ++phase) {
       ++seq;
@@ -940,7 +961,7 @@ __device__ __forceinline__ void persist_service(const RankDev& P, int niter) {
       if (lane == 0) {
         const long long t0 = clock64();
         while (ld_acquire_gpu(&S.gbar) < seq)
-          if (clock64() - t0 > 8 * S.timeout_cycles) {  // the working CTAs are gone (their waits are bounded, too)
+          if (clock64() - t0 > 8 * timeout) {  // the working CTAs are gone (their waits are bounded, too)
             if (atomicCAS(&S.dbg[0], 0, 12) == 0) {
               S.dbg[3] = (int)seq;
               S.dbg[5] = (int)*(volatile u64*)&S.gbar;
@@ -957,7 +978,6 @@ __device__ __forceinline__ void persist_service(const RankDev& P, int niter) {
         return;
       }
       unsigned long long t_local = 0;
-      const int tslot = __ldcg(&S.iter);
       if (P.trace && lane == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_local));
       double a = 0.0;
       const double2* part = P.partials + (seq & 1) * kPersistPartials;
@@ -965,44 +985,79 @@ __device__ __forceinline__ void persist_service(const RankDev& P, int niter) {
       a = warp_sum(a);                                                         // ... and a fixed tree across lanes
       bool ok = true;
       if (P.nranks > 1) {
-        const u64 rs = S.red_seq;
-        const int slot = (int)(rs & (kRedSlots - 1));
-        const unsigned tag = (unsigned)(rs + 1);
+        const int slot = (int)(red_seq & (kRedSlots - 1));
+        const unsigned tag = (unsigned)(red_seq + 1);
         double va = 0.0, vb = 0.0;
         if (lane < P.nranks) {
           ll_send2(&P.peer_ctrl[lane]->red_ll[slot][P.rank][0], a, 0.0, tag);
-          ok = ll_recv2(&P.ctrl->red_ll[slot][lane][0], tag, S.timeout_cycles, va, vb);
+          ok = ll_recv2(&P.ctrl->red_ll[slot][lane][0], tag, timeout, va, vb);
         }
         ok = __all_sync(0xffffffffu, ok);
         a = 0.0;
         for (int q = 0; q < P.nranks; ++q) a += __shfl_sync(0xffffffffu, va, q);   // rank order on every rank
       }
+      red_seq += 1;
+      const int tslot = iter;
+      int new_done = 0;
       if (lane == 0) {
-        S.last_sum[0] = a;
-        S.last_sum[1] = 0.0;
-        S.red_seq += 1;
+        // ---- what the working CTAs are waiting for, first ----
+        double rn = 0.0;
         if (!ok) {
-          S.done = CGB_ERR_TIMEOUT;
+          new_done = CGB_ERR_TIMEOUT;
         } else if (done) {
           // the speculative p.Ap of a finished solve (see persist_iteration): nothing to update
         } else if (phase == 0) {
-          S.pAp = a;
-          S.alpha = S.rho / a;
+          S.alpha = rho / a;   // CUDACG.cu:311
         } else {
-          cg_after_rr(P, a);
+          // the reference's test position and rule: absolute ||r||_2 < tol after the x/r update (CUDACG.cu:333)
+          rn = sqrt(a);
+          if (!isfinite(a)) {
+            new_done = CGB_ERR_BREAKDOWN;
+          } else if (rn < thresh) {
+            new_done = 1;
+          } else {
+            S.beta = a / rho;  // CUDACG.cu:339
+            if (iter + 1 >= maxit) new_done = 2;
+            else S.halo_seq = ++halo_seq;
+          }
         }
+        if (new_done != 0) S.done = new_done;
         __threadfence();
         st_release_gpu(&S.sbar, seq);
+        // ---- bookkeeping, off the critical path ----
+        S.last_sum[0] = a;
+        S.last_sum[1] = 0.0;
+        S.red_seq = red_seq;
+        if (ok && !done) {
+          if (phase == 0) {
+            S.pAp = a;
+          } else {
+            if (iter < P.hist_cap) P.hist[iter] = rn;
+            if (P.hist_host && iter < P.hist_host_cap) P.hist_host[iter] = rn;  // zero-copy D2H of this step's result
+            S.rnorm = rn;
+            S.iter = iter + 1;
+            if (new_done == 0 || new_done == 2) {
+              S.rho_prev = rho;
+              S.rho = a;
+            }
+          }
+        }
         if (P.trace && !done && tslot < P.trace_cap) {
           unsigned long long t_rel;
           asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_rel));
           P.trace[4 * tslot + 2 * phase] = t_local;
           P.trace[4 * tslot + 2 * phase + 1] = t_rel;
         }
+        if (ok && !done && phase == 1) {
+          if (new_done == 0 || new_done == 2) rho = a;
+          iter += 1;
+        }
       }
-      __syncwarp();
-      if (done) return;   // the working CTAs leave after this (speculative) barrier A, too
-      if (phase == 1) done = __shfl_sync(0xffffffffu, lane == 0 ? (int)(S.done != 0) : 0, 0) != 0;
+      const bool was_done = done;
+      done = __shfl_sync(0xffffffffu, (int)(done || new_done != 0), 0) != 0;
+      // finished as of the previous barrier: this was the speculative barrier A (see persist_iteration) and the
+      // working CTAs leave after it, too
+      if (phase == 0 && was_done) return;
     }
   }
 }
@@ -1219,6 +1274,31 @@ int spmv_tma_make_map(int kind, const cgb_layout_t& L, const double* vec, void* 
   return CGB_OK;
 }
 
+namespace {
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = std::getenv("CGB_PDL");   // measured on B200 (profiles/ROOFLINE.md): no gain at 512^3, so opt-in
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+// <<<>>> with the programmatic-stream-serialization attribute (see pdl_wait above).
+template <class... KArgs, class... Args>
+cudaError_t launch_band(void (*kernel)(KArgs...), int grid, size_t smem, cudaStream_t s, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)grid);
+  cfg.blockDim = dim3(kNT);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+}  // namespace
+
 cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const void* map_h, const void* map_x,
                             const void* map_r, double* out, int mode, cudaStream_t s) {
   static bool attr_set[64] = {};
@@ -1251,20 +1331,21 @@ cudaError_t launch_spmv_tma(const RankDev& P, int device, const void* map, const
   const CUtensorMap& tr = *reinterpret_cast<const CUtensorMap*>(map_r ? map_r : map);
   const int kd = P.st.kind;
   if (!kind_is_stencil(kd)) return cudaErrorInvalidValue;
+  cudaError_t e;
 #define CGB_TMA_LAUNCH(OUT)                                                                                   \
   do {                                                                                                        \
     if (kd == CGB_KIND_POISSON3D7)                                                                            \
-      k_spmv_tma<CGB_KIND_POISSON3D7, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);            \
+      e = launch_band(k_spmv_tma<CGB_KIND_POISSON3D7, OUT>, grid, sm, s, P, tm, th, tx, tr, G, out, mode);    \
     else if (kd == CGB_KIND_STENCIL3D27)                                                                      \
-      k_spmv_tma<CGB_KIND_STENCIL3D27, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);           \
+      e = launch_band(k_spmv_tma<CGB_KIND_STENCIL3D27, OUT>, grid, sm, s, P, tm, th, tx, tr, G, out, mode);   \
     else                                                                                                      \
-      k_spmv_tma<CGB_KIND_POISSON2D5, OUT><<<grid, kNT, sm, s>>>(P, tm, th, tx, tr, G, out, mode);            \
+      e = launch_band(k_spmv_tma<CGB_KIND_POISSON2D5, OUT>, grid, sm, s, P, tm, th, tx, tr, G, out, mode);    \
   } while (0)
   if (mode == kSpmvUpdate) CGB_TMA_LAUNCH(2);
   else if (mode == kSpmvAlphaNoStore) CGB_TMA_LAUNCH(1);
   else CGB_TMA_LAUNCH(0);
 #undef CGB_TMA_LAUNCH
-  return cudaGetLastError();
+  return e;
 }
 
 cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const maps[6], const double* pold, double* pnew,
@@ -1288,14 +1369,15 @@ cudaError_t launch_pspmv_tma(const RankDev& P, int device, const void* const map
   const CUtensorMap* m[6];
   for (int k = 0; k < 6; ++k) m[k] = reinterpret_cast<const CUtensorMap*>(maps[k] ? maps[k] : maps[k % 3]);
   if (P.st.kind == CGB_KIND_POISSON3D7)
-    k_pspmv_tma<CGB_KIND_POISSON3D7><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
-  else if (P.st.kind == CGB_KIND_STENCIL3D27)
-    k_pspmv_tma<CGB_KIND_STENCIL3D27><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
-  else if (P.st.kind == CGB_KIND_POISSON2D5)
-    k_pspmv_tma<CGB_KIND_POISSON2D5><<<grid, kNT, sm, s>>>(P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold, pnew, newbuf);
-  else
-    return cudaErrorInvalidValue;
-  return cudaGetLastError();
+    return launch_band(k_pspmv_tma<CGB_KIND_POISSON3D7>, grid, sm, s, P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold,
+                       pnew, newbuf);
+  if (P.st.kind == CGB_KIND_STENCIL3D27)
+    return launch_band(k_pspmv_tma<CGB_KIND_STENCIL3D27>, grid, sm, s, P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold,
+                       pnew, newbuf);
+  if (P.st.kind == CGB_KIND_POISSON2D5)
+    return launch_band(k_pspmv_tma<CGB_KIND_POISSON2D5>, grid, sm, s, P, *m[0], *m[1], *m[2], *m[3], *m[4], *m[5], G, pold,
+                       pnew, newbuf);
+  return cudaErrorInvalidValue;
 }
 
 // Per-device one-time set-up of the persistent kernel. The caller has made `device` current.

@@ -121,6 +121,7 @@ cgb_ctx::~cgb_ctx() {
   if (d_rowptr) cudaFree(d_rowptr);
   if (d_colind) cudaFree(d_colind);
   if (d_val) cudaFree(d_val);
+  if (d_rowblk) cudaFree(d_rowblk);
   if (h_scal) cudaFreeHost(h_scal);
   if (ev_begin) cudaEventDestroy(ev_begin);
   if (ev_end) cudaEventDestroy(ev_end);
@@ -244,6 +245,21 @@ extern "C" int cgb_ctx_create_csr(int32_t n, int64_t nnz, const int32_t* rowptr,
   c->P.csr_colind = c->d_colind;
   c->P.csr_val = c->d_val;
   c->P.csr_avg_nnz = (int)((nnz + n - 1) / n);
+  {  // row blocks of the streaming SpMV kernel
+    const std::vector<int> blk = csr_row_blocks(n, rowptr);
+    auto up = [&]() -> int {
+      CGB_CUDA(cudaMalloc(&c->d_rowblk, blk.size() * sizeof(int)));
+      CGB_CUDA(cudaMemcpy(c->d_rowblk, blk.data(), blk.size() * sizeof(int), cudaMemcpyHostToDevice));
+      return CGB_OK;
+    };
+    rc = up();
+    if (rc != 0) {
+      delete c;
+      return rc;
+    }
+    c->P.csr_rowblk = c->d_rowblk;
+    c->P.csr_nblk = (int)blk.size() - 1;
+  }
   *out = c;
   return CGB_OK;
 }
@@ -488,11 +504,9 @@ extern "C" int cgb_ctx_debug_print(cgb_ctx* c) {
   CGB_CUDA(cudaMemcpy(&s, &c->P.ctrl->s, sizeof(Scalars), cudaMemcpyDeviceToHost));
   std::fprintf(stderr,
                "[cgb rank %d] iter=%d done=%d maxit=%d rho=%.6e alpha=%.6e beta=%.6e rnorm=%.6e red_seq=%llu halo_seq=%llu "
-               "gbar=%llu sbar=%llu ticket=%u dbg={site=%d block=%d thread=%d %d %d %d %d %d | %08x %08x %08x %08x %08x %08x}\n",
+               "gbar=%llu sbar=%llu ticket=%u dbg={site=%d block=%d thread=%d bar=%d parity=%d gbar=%d sbar=%d %d}\n",
                c->part.rank, s.iter, s.done, s.maxit, s.rho, s.alpha, s.beta, s.rnorm, s.red_seq, s.halo_seq, s.gbar, s.sbar,
-               s.ticket_red, s.dbg[0], s.dbg[1], s.dbg[2], s.dbg[3], s.dbg[4], s.dbg[5], s.dbg[6], s.dbg[7], s.dbg[8], s.dbg[9], s.dbg[10],
-               s.dbg[11], s.dbg[12], s.dbg[13]);
-  std::fprintf(stderr, "[cgb rank %d] dbg[12..15] = %d %d %d %d\n", c->part.rank, s.dbg[12], s.dbg[13], s.dbg[14], s.dbg[15]);
+               s.ticket_red, s.dbg[0], s.dbg[1], s.dbg[2], s.dbg[3], s.dbg[4], s.dbg[5], s.dbg[6], s.dbg[7]);
   return CGB_OK;
 }
 
@@ -690,10 +704,10 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   CGB_CUDA(cudaSetDevice(c->device));
   c->opts = *o;
   if (c->opts.variant == CGB_VAR_AUTO) {
-    // measured on B200 (profiles/): for the 7-point stencil merged > recompute > fused; 27-point stays fused
-    const bool tma7 = c->tma_ok && (c->st.kind == CGB_KIND_POISSON3D7 || c->st.kind == CGB_KIND_POISSON2D5) &&
-                      o->spmv_impl != CGB_SPMV_SIMPLE;
-    c->opts.variant = !tma7 ? CGB_VAR_FUSED : (merged2_ok(c) ? CGB_VAR_MERGED2 : CGB_VAR_MERGED);
+    // measured on B200 (profiles/ROOFLINE.md): merged > recompute > fused for every stencil, the 27-point one
+    // included since its band kernels stopped spilling (partial-sum sweep)
+    const bool band = c->tma_ok && kind_is_stencil(c->st.kind) && o->spmv_impl != CGB_SPMV_SIMPLE;
+    c->opts.variant = !band ? CGB_VAR_FUSED : (merged2_ok(c) ? CGB_VAR_MERGED2 : CGB_VAR_MERGED);
   }
   if (c->opts.chunk < 1) c->opts.chunk = 25;
   if (c->opts.fixed_iters > 0) {
@@ -712,7 +726,11 @@ extern "C" int cgb_solve_prepare(cgb_ctx* c, const cgb_solve_opts_t* o) {
   const bool persist_ok = c->opts.variant == CGB_VAR_MERGED2 && cg_persist_supported(c->device);
   if (c->opts.persistent == 1 && !persist_ok)
     return fail(CGB_ERR_UNSUPPORTED, "the persistent kernel needs the merged variant and cooperative launch support");
-  c->use_persist = persist_ok && c->opts.persistent != -1;
+  // persistent == 0 (auto): measured on B200, the persistent kernel ties with the two-kernel driver on one GPU
+  // (its inner loops come out ~10 % longer from the compiler, which the saved launches and the hidden reductions
+  // only just pay back), so auto keeps two kernels per iteration unless CGB_PERSISTENT=1 says otherwise.
+  static const bool env_on = [] { const char* e = std::getenv("CGB_PERSISTENT"); return e && e[0] == '1'; }();
+  c->use_persist = persist_ok && (c->opts.persistent == 1 || (c->opts.persistent == 0 && env_on));
   if (c->use_persist) {  // nothing to capture: one cooperative launch runs a whole chunk
     CGB_CUDA(cg_persist_prepare(c->device));
     return CGB_OK;

@@ -26,6 +26,7 @@ struct cgb_ctx {
   int* d_rowptr = nullptr;    // CSR problems
   int* d_colind = nullptr;
   double* d_val = nullptr;
+  int* d_rowblk = nullptr;    // row blocks of the streaming CSR SpMV (single-rank CSR problems)
   long long csr_nnz = 0;
 
   void* peer_base[CGB_MAX_RANKS] = {};

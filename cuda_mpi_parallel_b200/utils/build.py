@@ -104,12 +104,34 @@ def build_core(force=False, verbose=False) -> Path:
     return LIB
 
 
+B4_EXE = ROOT / "bin" / "refstyle_b4"
+
+
 def build_baseline(force=False, verbose=False) -> Path:
     srcs = _sources(ROOT / "baseline" / "src") if (ROOT / "baseline" / "src").exists() else []
+    srcs = [s for s in srcs if not s.stem.endswith("_main")]
     if not srcs:
         return BASELINE_LIB
     _build_lib("baseline", srcs, BASELINE_LIB, link_extra=["-lcusparse", "-lcublas"], force=force, verbose=verbose)
     return BASELINE_LIB
+
+
+def build_b4(force=False, verbose=False) -> Path:
+    """The multi-GPU reference-style baseline B4 (cuSPARSE/cuBLAS + NCCL all-reduce + peer-copy halo) as a separate
+    executable: it links the SYSTEM libnccl, which must not share a process with the NCCL that torch bundles."""
+    src = ROOT / "baseline" / "src" / "ref_b4_main.cu"
+    if not src.exists():
+        return B4_EXE
+    B4_EXE.parent.mkdir(exist_ok=True)
+    newest = max(p.stat().st_mtime for p in [src, LIB, ROOT / "include" / "cgb200.h"])
+    if force or not B4_EXE.exists() or B4_EXE.stat().st_mtime < newest:
+        cmd = [nvcc(), *ARCH, "-O3", "-std=c++17", "-lineinfo", f"-I{ROOT / 'include'}", str(src), "-o", str(B4_EXE),
+               f"-L{LIBDIR}", "-lcgb200", "-lnccl", "-lcusparse", "-lcublas", "-lpthread",
+               "-Xlinker", "-rpath", "-Xlinker", "$ORIGIN/../cuda_mpi_parallel_b200/lib"]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"B4 baseline build failed:\n{r.stdout}{r.stderr}")
+    return B4_EXE
 
 
 def build_cli(force=False, verbose=False) -> Path:
@@ -131,6 +153,7 @@ def build_cli(force=False, verbose=False) -> Path:
 def build_all(force=False, verbose=False):
     build_core(force, verbose)
     build_baseline(force, verbose)
+    build_b4(force, verbose)
     build_cli(force, verbose)
     return LIB
 

@@ -178,10 +178,11 @@ typedef struct cgb_solve_opts_t {
   int32_t warm_start;    /* 0: x0 = 0 like the reference (CUDACG.cu:177-179, 247); 1: start from the x the
                             context holds (cgb_ctx_set_x0 or the previous solve): r0 = b - A x0. This is
                             also the restart path of a checkpoint (x + iteration count). */
-  int32_t persistent;    /* merged variant only. 0 (default): run the iteration loop inside ONE persistent cooperative
-                            kernel per chunk when the device supports cooperative launch - grid barrier and all-reduce
-                            on the device, no kernel boundary inside an iteration; 1: require it; -1: two kernels per
-                            iteration (captured in graphs) as in use_graph */
+  int32_t persistent;    /* merged variant only. 1: run the iteration loop inside ONE persistent cooperative kernel per
+                            chunk - grid barrier on the device, the all-reduces done by a service CTA off the critical
+                            path, no kernel boundary inside an iteration; -1: two kernels per iteration (captured in
+                            graphs); 0 (default): auto = -1 unless the environment says CGB_PERSISTENT=1 (on one B200
+                            the two are within 2 % of each other, see profiles/ROOFLINE.md) */
   void* stream;          /* cudaStream_t to run on; NULL = context stream */
 } cgb_solve_opts_t;
 void cgb_solve_opts_default(cgb_solve_opts_t* o);

@@ -18,6 +18,13 @@ def main():
     dims = [int(v) for v in sys.argv[3].split("x")]
     decomp = int(sys.argv[4]) if len(sys.argv) > 4 else 1
     variant = sys.argv[5] if len(sys.argv) > 5 else "fused"
+    # "merged+persist": persistent cooperative kernel; "fused+while": one conditional-WHILE graph per solve
+    variant, _, opt = variant.partition("+")
+    kw = {}
+    if opt == "persist":
+        kw["persistent"] = True
+    elif opt == "while":
+        kw["use_graph"] = "while"
     import torch
     import torch.distributed as dist
     from cuda_mpi_parallel_b200 import Problem, cpu_cg
@@ -45,7 +52,7 @@ def main():
         ok = True
         for v in ("fused", "pipelined", variant):
             sol.set_rhs(b_local)
-            res = sol.solve(fixed_iters=1500, variant=v, chunk=50)
+            res = sol.solve(fixed_iters=1500, variant=v, chunk=50, **(kw if v == variant else {}))
             h = sol.history(200).tolist()       # before round-off takes over
             g = [None] * world
             dist.all_gather_object(g, (res.iters, res.status, h))
@@ -69,10 +76,10 @@ def main():
         sol = CGSolver(prob, rank=rank, nranks=world, decomp=decomp)
         attach_torch_distributed(sol)
         sol.set_rhs(b_local)
-        res = sol.solve(tol=1e-8, chunk=5, variant=variant)
+        res = sol.solve(tol=1e-8, chunk=5, variant=variant, **kw)
         # second solve on the same fabric: sequence numbers keep growing, history must repeat bitwise
         h1 = sol.history(res.iters)
-        res2 = sol.solve(tol=1e-8, chunk=8, variant=variant)
+        res2 = sol.solve(tol=1e-8, chunk=8, variant=variant, **kw)
         assert res2.iters == res.iters and (sol.history(res.iters) == h1).all(), "repeat solve differs"
         iters, hist, status = res.iters, h1, res.status
         x_local = sol.x().cpu().numpy()

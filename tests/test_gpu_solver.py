@@ -155,6 +155,7 @@ def test_recompute_variant_rejects_unsupported_problems():
 def test_merged_variant_matches_oracle(prob, persistent):
     # 64 B/DOF variant: p-update folded into the SpMV (halo rows recomputed in shared memory); either as ONE
     # persistent cooperative kernel per chunk (grid barrier + reduction on the device) or as two kernels per iteration.
+    # The persistent kernel sums the per-CTA partials in a different (still fixed) order: equal to rounding, not bitwise.
     b = prob.rhs("random", seed=19)
     ref = cpu_cg(prob, b, tol=1e-8)
     s = CGSolver(prob)

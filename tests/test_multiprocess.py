@@ -110,3 +110,38 @@ def test_gpu_distributed_general_csr(name, dims):
     nproc = 2 if n < 4 else 4
     res = _run(nproc, ["gpu", name, dims, "1", "fused"], port=29790, timeout=240)
     assert res["ok"] and res["ranks_identical"], res
+
+
+# ---- tiers that use every GPU of the box (8 on the B200 node): T3 partition invariance at full width ----
+
+def _all_gpus(minimum):
+    n = _ngpu()
+    if n < minimum:
+        pytest.skip(f"needs >= {minimum} GPUs")
+    return min(n, 8)
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("name,dims,decomp,variant", [
+    ("poisson3d7", "64x48x64", 1, "merged"), ("poisson3d7", "64x48x64", 1, "merged+persist"),
+    ("stencil3d27", "48x40x64", 1, "merged"), ("stencil3d27", "48x40x64", 1, "merged+persist"),
+    ("poisson2d5", "200x160", 1, "merged+persist"), ("poisson3d7", "1030x8x64", 1, "merged+persist"),
+    ("poisson3d7", "48x64x64", 2, "recompute"), ("stencil3d27", "40x64x64", 2, "fused"),
+    ("stencil3d27", "40x64x64", 2, "pipelined"), ("poisson3d7", "64x48x64", 1, "fused+while"),
+    ("poisson3d7", "64x48x64", 1, "merged+while")])
+def test_gpu_fabric_all_gpus(name, dims, decomp, variant):
+    # every visible GPU (8 ranks on the B200 box): z slabs, 2x4 pencils (decomp=2), the persistent kernel, and the
+    # conditional-WHILE graph at N > 1
+    nproc = _all_gpus(2)
+    res = _run(nproc, ["gpu", name, dims, str(decomp), variant], port=29810 + decomp, timeout=300)
+    assert res["ok"] and res["ranks_identical"] and res["world"] == nproc, res
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+@pytest.mark.parametrize("variant", ["merged", "merged+persist"])
+def test_gpu_fabric_soak_all_gpus(variant):
+    nproc = _all_gpus(2)
+    res = _run(nproc, ["soak", "poisson3d7", "32x16x64", "1", variant], port=29830, timeout=300)
+    assert res["ok"] and res["world"] == nproc, res
