@@ -8,13 +8,18 @@
 A "step" is one CG iteration (SpMV + both dot products + all vector updates + halo exchange +
 all-reduces).  The grid is fixed at 512^3 for every GPU count (strong scaling), 1D z-slab
 decomposition.  Timing: CUDA events on the launching stream bracketed by barrier +
-synchronize, max over ranks.  Every vector is far larger than the 126 MB L2 (1.07 GB per vector at
-N=1, 134 MB per vector and 5 vectors per rank at N=8), so no explicit L2 flush is needed.
+synchronize, max over ranks.  An iteration streams 8 vector passes of 134 MB (N=8) to 1.07 GB (N=1)
+per rank through the 126 MB L2, so no explicit L2 flush is needed.  The JSON line carries the
+residual after the timed iterations of a deterministic RHS (`rnorm_after_steps`): it must not
+depend on the number of GPUs.
 
-`--impl reference` would have to run the unmodified reference (CUDACG.cu) on this configuration; the
-reference is a single `main()` hard-wired to one 3x3 system with no problem-size input, so that arm
+Arms.  `--impl reference` would have to run the unmodified reference (CUDACG.cu) on this configuration;
+the reference is a single `main()` hard-wired to one 3x3 system with no problem-size input, so that arm
 prints {"impl":"reference","unavailable":...}.  `--impl refstyle` runs OUR restatement of the
-reference's cuSPARSE/cuBLAS call sequence (baseline/), labelled as such.
+reference's cuSPARSE/cuBLAS call sequence (baseline/): B3 on one GPU, B4 (+ ncclAllReduce +
+cudaMemcpyPeerAsync halo) on N GPUs, labelled as such.  `--problem csr7` races our general-CSR path
+against `--impl refstyle --problem csr7` on the same assembled matrix (the reference's own capability).
+`--persistent on|off`, `--trace`: the persistent cooperative kernel and its per-iteration time budget.
 """
 from __future__ import annotations
 

@@ -150,3 +150,23 @@ def test_python_module_cli_gpu(tmp_path):
     meta = json.loads(j.read_text())
     prob = Problem.poisson3d(48)
     assert meta["status"] == 1 and abs(meta["iters"] - cpu_cg(prob, prob.rhs("ones")).iters) <= 1
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_gpu_distributed_csr_from_the_cli(cli, tmp_path):
+    # `--problem csr:<file> --gpus N`: the general-CSR capability of the reference, row-block distributed over N GPUs
+    import scipy.io
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    P = 4 if torch.cuda.device_count() >= 4 else 2
+    prob = Problem.poisson3d(14, 12, 10)
+    A = prob.to_scipy()
+    m = tmp_path / "poisson.mtx"
+    scipy.io.mmwrite(str(m), A, symmetry="general")
+    xo = tmp_path / "x.txt"
+    r = run(cli, "--problem", f"csr:{m}", "--gpus", str(P), "--tol", "1e-9", "--no-print-x", "--x-out", str(xo))
+    assert r.returncode == 0 and r.stdout == "Success\n", r.stdout + r.stderr
+    x = np.loadtxt(xo)
+    np.testing.assert_allclose(A @ x, np.ones(prob.n), atol=1e-7)

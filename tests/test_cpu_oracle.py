@@ -90,3 +90,19 @@ def test_problem_from_scipy_and_matrix_market(tmp_path):
     s = cpu_cg(p1, b, tol=1e-10)
     assert s.converged
     np.testing.assert_allclose(p1.to_scipy() @ s.x, b, atol=1e-8)
+
+
+def test_rhs_fill_box_matches_the_per_entry_generator_and_partitions():
+    # cgb_rhs_fill_box is what bench.py stages into pinned memory for the end-to-end arm: it must equal the
+    # per-entry generator (and hence the device generator) for every rank's box, whatever the decomposition.
+    import ctypes as C
+    from cuda_mpi_parallel_b200 import Problem, _native as N
+    from cuda_mpi_parallel_b200.parallel.partition import gather_global, make_partition
+    for prob in (Problem.poisson3d(7, 6, 9), Problem.poisson2d(11, 8), Problem.stencil27(5, 8, 6)):
+        g = prob.rhs("random", seed=3)
+        ref = np.array([N.lib().cgb_rhs_value(C.byref(prob.stencil), N.RHS_RANDOM, 3, i) for i in range(prob.n)])
+        np.testing.assert_array_equal(g, ref)
+        for nranks, decomp in ((3, 1), (4, 2 if prob.name != "poisson2d5" else 1)):
+            parts = [make_partition(prob, nranks, r, decomp) for r in range(nranks)]
+            locs = [prob.rhs_local(p, "random", seed=3) for p in parts]
+            np.testing.assert_array_equal(gather_global(prob, parts, locs), g)

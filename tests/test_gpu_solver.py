@@ -309,3 +309,26 @@ def test_iterate_streamed_copies_each_residual_to_pinned_memory():
         res = s.finish()
     assert res.iters == 12
     np.testing.assert_array_equal(hist.numpy(), s.history(12))
+
+
+def test_poll_without_wait_never_blocks_and_catches_up():
+    # cgb_solve_poll(wait=0) returns the newest snapshot whose copy has landed and never synchronises the stream
+    import ctypes as C
+    import time
+    from cuda_mpi_parallel_b200 import _native as N
+    prob = Problem.poisson3d(96, 96, 96)
+    s = CGSolver(prob)
+    s.set_rhs("random", seed=5)
+    s.begin(fixed_iters=300, chunk=50)
+    s.iterate(300)
+    r = N.SolveResult()
+    seen = []
+    for _ in range(2000):
+        N.check(N.lib().cgb_solve_poll(s._ctx, 0, C.byref(r)))
+        seen.append(r.iters)
+        if r.iters == 300:
+            break
+        time.sleep(0.001)
+    assert seen == sorted(seen) and seen[-1] == 300, seen[-5:]
+    res = s.finish()
+    assert res.iters == 300
