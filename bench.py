@@ -52,7 +52,8 @@ def parse():
     ap.add_argument("--decomp", type=int, default=1)
     ap.add_argument("--chunk", type=int, default=0)
     ap.add_argument("--persistent", default="auto", choices=["auto", "on", "off"],
-                    help="merged variant: one persistent cooperative kernel per chunk (auto/on) or two kernels per iteration (off)")
+                    help="merged variant: one persistent cooperative kernel per chunk (on) or two kernels per iteration "
+                         "(off); auto = two kernels unless CGB_PERSISTENT=1")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--trace", action="store_true",
                     help="persistent kernel: record device timestamps at both barriers of every iteration and add a "

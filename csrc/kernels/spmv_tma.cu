@@ -1197,9 +1197,27 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
   if (G.nstages < 2) return false;
   const size_t sm = (size_t)G.nstages * G.stage_bytes;
   const int capacity = nsm;  // 544 threads x ~96 registers: one CTA per SM
+  // z split. One round (every CTA sweeps one item) is the default; when that leaves many SMs idle or the last round
+  // mostly empty (96 bands on 148 SMs, 512 bands = 3.46 rounds), a finer split with several items per CTA is chosen
+  // from the length of the longest CTA: rounds x (planes per item + the 2 planes an item loads without emitting).
+  // The finer split re-reads 2 planes per item, so it has to promise > 12 % before it replaces the default.
+  const int zs_max = L.nz / 8 > 1 ? L.nz / 8 : 1;
   int zs = capacity / G.nbands;
-  if (zs > L.nz / 8) zs = L.nz / 8;
+  if (zs > zs_max) zs = zs_max;
   if (zs < 1) zs = 1;
+  {
+    auto cost = [&](int z) {
+      const int zc = (L.nz + z - 1) / z, ze = (L.nz + zc - 1) / zc;
+      const long long items = (long long)G.nbands * ze;
+      return ((items + capacity - 1) / capacity) * (long long)(zc + 2);
+    };
+    static const int forced = [] { const char* e = std::getenv("CGB_ZSPLIT"); return e ? std::atoi(e) : 0; }();
+    int best = zs;
+    for (int z = 1; z <= zs_max && z <= 256; ++z)
+      if (cost(z) < cost(best)) best = z;
+    if (cost(best) * 100 < cost(zs) * 88) zs = best;
+    if (forced > 0) zs = forced < zs_max ? forced : zs_max;
+  }
   G.zchunk = (L.nz + zs - 1) / zs;
   G.zs = (L.nz + G.zchunk - 1) / G.zchunk;
   const bool nb_lo = P.nbr[dir_index(0, -1)] >= 0, nb_hi = P.nbr[dir_index(0, 1)] >= 0;

@@ -228,8 +228,8 @@ class CGSolver:
               stream=None, warm_start: bool = False, persistent=None) -> SolveResult:
         """warm_start: start from the x the solver holds (``set_x0`` / ``load_checkpoint`` / the previous solve)
         instead of the reference's x0 = 0: r0 = b - A x0.
-        persistent (merged variant): None = one persistent cooperative kernel per chunk where supported,
-        True = require it, False = two kernels per iteration."""
+        persistent (merged variant): None = two kernels per iteration unless CGB_PERSISTENT=1 is set,
+        True = require the persistent cooperative kernel (one launch per chunk), False = never use it."""
         o = self._fill_opts(tol, maxit, tol_mode, variant, spmv, use_graph, chunk, fixed_iters, stream, warm_start,
                             persistent)
         r = N.SolveResult()
