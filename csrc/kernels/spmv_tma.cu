@@ -65,6 +65,8 @@ struct BandGeo {
   int nstages;
   int nhalo;         // merged kernel: extra CTAs (on otherwise idle SMs) that only push the boundary planes
   int nctas;         // CTAs that sweep bands (= grid - nhalo); items are dealt round-robin over these
+  int wide;          // 2D grids whose rows are a multiple of 256 cells: the main maps describe a row as (256, nx/256)
+                     // so that ONE TMA operation brings the whole x tile of a row (NBX boxes) instead of NBX
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -495,19 +497,25 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
           const bool with_xr = OUT == 2 && s >= 2;  // this step emits a plane: bring its x and r rows too
           mbar_expect_tx(full0 + 8 * st, p_tx + (with_xr ? 2u * (unsigned)G.xr_bytes : 0u));
           const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
-          for (int b = 0; b < G.NBX; ++b)
-            tma_load_3d(dst + b * G.prow * BW * 8, tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+          if (G.wide) tma_load_3d(dst, tmap, 0, it.x0 / BW, q + 1, full0 + 8 * st);
+          else
+            for (int b = 0; b < G.NBX; ++b)
+              tma_load_3d(dst + b * G.prow * BW * 8, tmap, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
           if (G.ntx > 1) {  // the tile's x halo: two 2-column boxes (zero-filled outside the domain)
             tma_load_3d(dst + G.h_off, tmap_h, it.x0 - 2, y0, q + 1, full0 + 8 * st);
             tma_load_3d(dst + G.h_off + 128, tmap_h, it.x0 + 2 * G.LX, y0, q + 1, full0 + 8 * st);
           }
           if (with_xr) {
             const int ko = it.dir > 0 ? it.k0 + s - 2 : it.k1 - s + 1;
-            for (int b = 0; b < G.NBX; ++b) {
-              tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, tmx, it.x0 + b * BW, y0 + G.HY, ko + 1, full0 + 8 * st);
-              tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, tmr, it.x0 + b * BW, y0 + G.HY, ko + 1,
-                          full0 + 8 * st);
-            }
+            if (G.wide) {
+              tma_load_3d(dst + G.p_bytes, tmx, 0, it.x0 / BW, ko + 1, full0 + 8 * st);
+              tma_load_3d(dst + G.p_bytes + G.xr_bytes, tmr, 0, it.x0 / BW, ko + 1, full0 + 8 * st);
+            } else
+              for (int b = 0; b < G.NBX; ++b) {
+                tma_load_3d(dst + G.p_bytes + b * G.RB * BW * 8, tmx, it.x0 + b * BW, y0 + G.HY, ko + 1, full0 + 8 * st);
+                tma_load_3d(dst + G.p_bytes + G.xr_bytes + b * G.RB * BW * 8, tmr, it.x0 + b * BW, y0 + G.HY, ko + 1,
+                            full0 + 8 * st);
+              }
           }
         }
       }
@@ -649,10 +657,14 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
     mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 3);
     mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
     const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
-    for (int b = 0; b < G.NBX; ++b) {
-      tma_load_3d(dst + b * boxb, ghost ? tm_pnew : tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
-      tma_load_3d(dst + G.p_bytes + b * boxb, tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
-    }
+    if (G.wide) {
+      tma_load_3d(dst, ghost ? tm_pnew : tm_r, 0, it.x0 / BW, q + 1, full0 + 8 * st);
+      tma_load_3d(dst + G.p_bytes, tm_pold, 0, it.x0 / BW, q + 1, full0 + 8 * st);
+    } else
+      for (int b = 0; b < G.NBX; ++b) {
+        tma_load_3d(dst + b * boxb, ghost ? tm_pnew : tm_r, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+        tma_load_3d(dst + G.p_bytes + b * boxb, tm_pold, it.x0 + b * BW, y0, q + 1, full0 + 8 * st);
+      }
     if (G.ntx > 1) {
       const int xl = it.x0 - 2, xr = it.x0 + 2 * G.LX;
       tma_load_3d(dst + G.h_off, ghost ? tm_pnew_h : tm_r_h, xl, y0, q + 1, full0 + 8 * st);
@@ -1168,6 +1180,12 @@ EncodeFn get_encode() {
   return fn;
 }
 
+// 2D grids (one row per plane, no y padding) whose rows are whole 256-cell boxes and are stored without pitch padding.
+bool wide_rows(int kind, const cgb_layout_t& L) {
+  static const bool off = [] { const char* e = std::getenv("CGB_TMA_NARROW"); return e && e[0] == '1'; }();
+  return !off && !kind_has_y_taps(kind) && L.py == 1 && L.nx % box_w(kind) == 0 && L.pitch == L.nx;
+}
+
 bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size_t* smem) {
   const cgb_layout_t& L = P.lay;
   if (!kind_is_stencil(P.st.kind)) return false;
@@ -1184,6 +1202,7 @@ bool make_geo(const RankDev& P, int nsm, int mode, BandGeo* out, int* grid, size
   G.prow = G.RB + 2 * G.HY;
   const int BW = box_w(P.st.kind);
   G.NBX = (tile + BW - 1) / BW;
+  G.wide = wide_rows(P.st.kind, L) ? 1 : 0;
   G.nby = (L.ny + G.RB - 1) / G.RB;
   G.nbands = G.ntx * G.nby;
   G.h_off = G.NBX * G.prow * BW * 8;                  // halo boxes sit behind the main boxes
@@ -1284,6 +1303,12 @@ int spmv_tma_make_map(int kind, const cgb_layout_t& L, const double* vec, void* 
   cuuint64_t strides[2] = {(cuuint64_t)L.pitch * 8, (cuuint64_t)L.pitch * L.py * 8};
   if (box_cols != 2) box_cols = box_w(kind);  // main boxes; 2 = the x-halo boxes of tiled rows
   cuuint32_t box[3] = {(cuuint32_t)box_cols, (cuuint32_t)(halo_rows ? G.prow : G.RB), 1};
+  if (G.wide && box_cols != 2) {  // a row seen as nx/256 lines of 256 cells: one box = the x tile of one row
+    dims[0] = (cuuint64_t)box_cols;
+    dims[1] = (cuuint64_t)(L.nx / box_cols);
+    strides[0] = (cuuint64_t)box_cols * 8;
+    box[1] = (cuuint32_t)G.NBX;
+  }
   cuuint32_t es[3] = {1, 1, 1};
   CUresult r = enc((CUtensorMap*)map_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<double*>(vec), dims, strides,
                    box, es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,

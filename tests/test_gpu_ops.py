@@ -12,6 +12,8 @@ PROBLEMS = [
     Problem.stencil27(9, 6, 5), Problem.stencil27(70, 21, 35), Problem.stencil27(64, 64, 40),
     Problem.poisson3d(1030, 7, 5), Problem.stencil27(1537, 6, 4),      # rows wider than one 512-cell TMA tile
     Problem.poisson2d(2300, 9),                                        # 2D rows wider than one 1024-cell tile
+    Problem.poisson2d(256, 40), Problem.poisson2d(1024, 33),           # 2D rows of whole 256-cell boxes: one TMA op per row
+    Problem.poisson2d(2304, 21),                                       # ... 3 tiles, the last one mostly out of bounds
 ]
 
 

@@ -278,7 +278,8 @@ def test_x_tiled_rows_all_variants(prob, variant):
 
 
 @pytest.mark.parametrize("variant", ["fused", "recompute", "merged", "pipelined"])
-@pytest.mark.parametrize("prob", [Problem.poisson2d(200, 90), Problem.poisson2d(33, 17), Problem.poisson2d(2300, 12)],
+@pytest.mark.parametrize("prob", [Problem.poisson2d(200, 90), Problem.poisson2d(33, 17), Problem.poisson2d(2300, 12),
+                                  Problem.poisson2d(512, 40), Problem.poisson2d(2304, 24)],
                          ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
 def test_2d_problems_on_the_tma_kernels(prob, variant):
     # a 2D grid is a one-row-per-plane 3D grid: same band kernels, no y taps

@@ -127,6 +127,7 @@ def _all_gpus(minimum):
     ("poisson3d7", "64x48x64", 1, "merged"), ("poisson3d7", "64x48x64", 1, "merged+persist"),
     ("stencil3d27", "48x40x64", 1, "merged"), ("stencil3d27", "48x40x64", 1, "merged+persist"),
     ("poisson2d5", "200x160", 1, "merged+persist"), ("poisson3d7", "1030x8x64", 1, "merged+persist"),
+    ("poisson2d5", "1280x160", 1, "merged"), ("poisson2d5", "512x128", 1, "merged+persist"),
     ("poisson3d7", "48x64x64", 2, "recompute"), ("stencil3d27", "40x64x64", 2, "fused"),
     ("stencil3d27", "40x64x64", 2, "pipelined"), ("poisson3d7", "64x48x64", 1, "fused+while"),
     ("poisson3d7", "64x48x64", 1, "merged+while")])
