@@ -139,6 +139,17 @@ __device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map
       : "memory");
 }
 
+// A 2D grid is one row per plane: the second row of a thread's 2x2 patch does not exist.
+template <int KIND> constexpr bool kTwoRows = KIND != CGB_KIND_POISSON2D5;
+
+// Next slot of the stage ring (st) and its mbarrier phase parity (ph).
+__device__ __forceinline__ void ring_next(unsigned& st, unsigned& ph, unsigned nstages) {
+  if (++st == nstages) {
+    st = 0;
+    ph ^= 1u;
+  }
+}
+
 struct PS2 {  // plane sums of one cell pair
   double s0[2], s1[2], s2[2];
 };
@@ -172,6 +183,9 @@ __device__ __forceinline__ Taps make_taps(const BandGeo& G, int il, int i, int n
   } else {
     tp.r = col + 2 == BW ? (b + 1) * boxb : tp.c + 16;
   }
+  // Opaque to the optimiser: otherwise ptxas may re-derive ls/rs (selects on ntx, il) at every tap of every plane
+  // instead of keeping five integers, which costs ~100 instructions per plane in the 27-point loops.
+  asm volatile("" : "+r"(tp.c), "+r"(tp.l), "+r"(tp.r), "+r"(tp.ls), "+r"(tp.rs));
   return tp;
 }
 
@@ -483,16 +497,17 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
         asm volatile("fence.proxy.async;" ::: "memory");
         waited = true;
       };
+      // ring position of step n, advanced without a division per step (kStages is a run-time value)
+      unsigned st = n % kStages, ph = (n / kStages) & 1u;
       for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
         if (it.y_ghost) wait_flags();
         const int y0 = it.yb * G.RB;  // padded row of band row -1
         const int nsteps = it.k1 - it.k0 + 2;
         const unsigned p_tx = (unsigned)(G.NBX * G.prow * BW * 8 + (G.ntx > 1 ? 2 * G.prow * 16 : 0));
-        for (int s = 0; s < nsteps; ++s, ++n) {
+        for (int s = 0; s < nsteps; ++s, ++n, ring_next(st, ph, kStages)) {
           const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
           if ((q == -1 && nb_zlo) || (q == L.nz && nb_zhi)) wait_flags();
-          const unsigned st = n % kStages, ph = (n / kStages) & 1u;
           mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 1);
           const bool with_xr = OUT == 2 && s >= 2;  // this step emits a plane: bring its x and r rows too
           mbar_expect_tx(full0 + 8 * st, p_tx + (with_xr ? 2u * (unsigned)G.xr_bytes : 0u));
@@ -523,33 +538,36 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
   } else {
     // ===== consumer warps =====
     const int lx = tid % G.LX, ly = tid / G.LX;
-    const int il = 2 * lx;
-    const int ra = 2 * ly;
-    const int xr_off = (il / BW) * (G.RB * BW * 8) + (ra * BW + il % BW) * 8;
+    unsigned st = n % kStages, ph = (n / kStages) & 1u;
     for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, nb_ylo, nb_yhi);
+      // A thread without cells (beyond the row end of the last x tile, or in a row pair the band does not have)
+      // shadows thread 0: its loads stay inside the slab and the plane loop needs no branch around them; jend = 0
+      // keeps it from storing or accumulating anything.
+      const bool active = ly < G.LY && it.x0 + 2 * lx < L.nx;
+      const int il = active ? 2 * lx : 0;
+      const int ra = active ? 2 * ly : 0;
+      const int xr_off = (il / BW) * (G.RB * BW * 8) + (ra * BW + il % BW) * 8;
       const int i = it.x0 + il;
-      const bool active = ly < G.LY && i < L.nx;
       const Taps tp = make_taps<BW>(G, il, i, L.nx);
       const int ja = it.yb * G.RB + ra;
       const int jend = active ? min(L.ny, (it.yb + 1) * G.RB) : 0;
-      const bool va = ja < jend, vb = ja + 1 < jend, pair = i + 1 < L.nx;
+      const bool va = ja < jend, vb = kTwoRows<KIND> && ja + 1 < jend, pair = i + 1 < L.nx;
       const int nsteps = it.k1 - it.k0 + 2;
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;           // signed plane stride along the sweep
       // index of (i, ja) on the plane emitted at step 2, then advanced by ps per step
       int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);
       Run2 A{}, B{};
-      for (int s = 0; s < nsteps; ++s, ++n) {
-        const unsigned st = n % kStages, ph = (n / kStages) & 1u;
+      for (int s = 0; s < nsteps; ++s, ++n, ring_next(st, ph, kStages)) {
         mbar_wait(full0 + 8 * st, ph, S, 2);
         const unsigned char* stage = smem_raw + (size_t)st * G.stage_bytes;
-        PS2 na{}, nb{};
-        if (active) plane_from_slab<KIND>(stage, tp, ra, na, nb);
-        double ca[2], ta[2], cb[2], tb[2];
+        PS2 na, nb;
+        plane_from_slab<KIND>(stage, tp, ra, na, nb);
+        double ca[2], ta[2], cb[2] = {0, 0}, tb[2] = {0, 0};
         plane_ct<KIND>(P, na, ca, ta);
-        plane_ct<KIND>(P, nb, cb, tb);
+        if (kTwoRows<KIND>) plane_ct<KIND>(P, nb, cb, tb);
         double2 cxa = make_double2(0, 0), cxb = cxa, cra = cxa, crb = cxa;
-        if (OUT == 2 && s >= 2 && active) {  // x and r rows of the plane emitted now (TMA-staged)
+        if (OUT == 2 && s >= 2) {  // x and r rows of the plane emitted now (TMA-staged)
           const unsigned char* xs = stage + G.p_bytes + xr_off;
           cxa = *reinterpret_cast<const double2*>(xs);
           cra = *reinterpret_cast<const double2*>(xs + G.xr_bytes);
@@ -567,11 +585,11 @@ __device__ __forceinline__ void phase_spmv(const RankDev& P, const BandGeo& G, c
             lazy = false;
           }
           if (va) emit<KIND, OUT>(P, out, A, ta, idx, pair, alpha, cxa, cra, acc);
-          if (vb) emit<KIND, OUT>(P, out, B, tb, idx + L.pitch, pair, alpha, cxb, crb, acc);
+          if (kTwoRows<KIND> && vb) emit<KIND, OUT>(P, out, B, tb, idx + L.pitch, pair, alpha, cxb, crb, acc);
           idx += ps;
         }
         run_advance<KIND>(P, A, na, ca, ta);
-        run_advance<KIND>(P, B, nb, cb, tb);
+        if (kTwoRows<KIND>) run_advance<KIND>(P, B, nb, cb, tb);
       }
     }
   }
@@ -648,12 +666,11 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
   unsigned n = R.n;
 
   // One slab (r or ghost p_new, plus p_old) of step s of an item into its ring stage. TMA lane only.
-  auto issue = [&](const Item& it, int s, unsigned nn) {
+  auto issue = [&](const Item& it, int s, unsigned st, unsigned ph) {
     const int y0 = it.yb * G.RB;
     const unsigned p_tx = (unsigned)(G.NBX * boxb + (G.ntx > 1 ? 2 * G.prow * 16 : 0));
     const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
     const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
-    const unsigned st = nn % kStages, ph = (nn / kStages) & 1u;
     mbar_wait(empty0 + 8 * st, ph ^ 1u, S, 3);
     mbar_expect_tx(full0 + 8 * st, 2u * p_tx);
     const unsigned dst = smem_u32(smem_raw + (size_t)st * G.stage_bytes);
@@ -687,8 +704,10 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
     if (tid == kNC && item0 < G.nitems && !(P.dbg_flags & 1)) {
       const Item it = make_item(P, G, item0, nb_zlo, nb_zhi, false, false);
       const int nsteps = it.k1 - it.k0 + 2;
+      unsigned st = n % kStages, ph = (n / kStages) & 1u;
       while (prefetched < nsteps && prefetched < (int)kStages && !is_ghost_step(it, prefetched)) {
-        issue(it, prefetched, n + (unsigned)prefetched);
+        issue(it, prefetched, st, ph);
+        ring_next(st, ph, kStages);
         ++prefetched;
       }
     }
@@ -752,13 +771,14 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
   if (warp == kNC / 32) {
     if (lane == 0) {
       bool waited = false;
+      n += (unsigned)prefetched;   // slabs of the first item that are already in flight
+      unsigned st = n % kStages, ph = (n / kStages) & 1u;
       for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
         const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
         const int nsteps = it.k1 - it.k0 + 2;
-        int s = prefetched;   // slabs of the first item that are already in flight
-        n += (unsigned)prefetched;
+        int s = prefetched;
         prefetched = 0;
-        for (; s < nsteps; ++s, ++n) {
+        for (; s < nsteps; ++s, ++n, ring_next(st, ph, kStages)) {
           if (is_ghost_step(it, s) && !waited) {
             for (int d = 0; d < CGB_NDIR; ++d)
               if (d != 4 && P.nbr[d] >= 0 && !spin_until_ge(&P.ctrl->halo_flag[d], version, S.timeout_cycles))
@@ -766,41 +786,41 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
             asm volatile("fence.proxy.async;" ::: "memory");
             waited = true;
           }
-          issue(it, s, n);
+          issue(it, s, st, ph);
         }
       }
     }
   } else {
     const int lx = tid % G.LX, ly = tid / G.LX;
-    const int il = 2 * lx;
-    const int ra = 2 * ly;
+    unsigned st = n % kStages, ph = (n / kStages) & 1u;
     for (int item = bid < (unsigned)G.nctas ? (int)bid : G.nitems; item < G.nitems; item += G.nctas) {
       const Item it = make_item(P, G, item, nb_zlo, nb_zhi, false, false);
+      const bool active = ly < G.LY && it.x0 + 2 * lx < L.nx;   // idle threads shadow thread 0, see phase_spmv
+      const int il = active ? 2 * lx : 0;
+      const int ra = active ? 2 * ly : 0;
       const int i = it.x0 + il;
-      const bool active = ly < G.LY && i < L.nx;
       const bool pair = i + 1 < L.nx;
       const Taps tp = make_taps<BW>(G, il, i, L.nx);
       const int ja = it.yb * G.RB + ra;
       const int jend = active ? min(L.ny, (it.yb + 1) * G.RB) : 0;
-      const bool va = ja < jend, vb = ja + 1 < jend;
+      const bool va = ja < jend, vb = kTwoRows<KIND> && ja + 1 < jend;
       const int nsteps = it.k1 - it.k0 + 2;
       const int64_t ps = (int64_t)L.pitch * L.py * it.dir;
       int64_t idx = lay_index(L, i, ja, it.dir > 0 ? it.k0 : it.k1 - 1);   // plane emitted at step 2
       int64_t gq = lay_index(L, i, ja, it.dir > 0 ? it.k0 - 1 : it.k1);    // plane loaded at step 0
       Run2 A{}, B{};
-      for (int s = 0; s < nsteps; ++s, ++n) {
-        const unsigned st = n % kStages, ph = (n / kStages) & 1u;
+      for (int s = 0; s < nsteps; ++s, ++n, ring_next(st, ph, kStages)) {
         const int q = it.dir > 0 ? it.k0 - 1 + s : it.k1 - s;
         const bool ghost = (q == -1 && nb_zlo) || (q == L.nz && nb_zhi);
-        const bool inb = q >= 0 && q < L.nz;
+        const bool inb = s >= 1 && s <= nsteps - 2;   // the item's own planes: the two outer slabs belong to others
         mbar_wait(full0 + 8 * st, ph, S, 4);
         const unsigned char* rs = smem_raw + (size_t)st * G.stage_bytes;
         double2 pna = make_double2(0, 0), pnb = pna;
-        PS2 na{}, nb{};
-        if (active) plane_from_two<KIND>(rs, rs + G.p_bytes, tp, ra, beta, ghost, na, nb, pna, pnb);
-        double ca[2], ta[2], cb[2], tb[2];
+        PS2 na, nb;
+        plane_from_two<KIND>(rs, rs + G.p_bytes, tp, ra, beta, ghost, na, nb, pna, pnb);
+        double ca[2], ta[2], cb[2] = {0, 0}, tb[2] = {0, 0};
         plane_ct<KIND>(P, na, ca, ta);
-        plane_ct<KIND>(P, nb, cb, tb);
+        if (kTwoRows<KIND>) plane_ct<KIND>(P, nb, cb, tb);
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * st);
         if (inb) {  // my two rows of p_new on the plane just loaded
@@ -817,11 +837,11 @@ __device__ __forceinline__ void phase_pspmv(const RankDev& P, const BandGeo& G, 
         if (s >= 2) {
           const double2 z2 = make_double2(0, 0);
           if (va) emit<KIND, 1>(P, nullptr, A, ta, idx, pair, 0.0, z2, z2, acc);
-          if (vb) emit<KIND, 1>(P, nullptr, B, tb, idx + L.pitch, pair, 0.0, z2, z2, acc);
+          if (kTwoRows<KIND> && vb) emit<KIND, 1>(P, nullptr, B, tb, idx + L.pitch, pair, 0.0, z2, z2, acc);
           idx += ps;
         }
         run_advance<KIND>(P, A, na, ca, ta);
-        run_advance<KIND>(P, B, nb, cb, tb);
+        if (kTwoRows<KIND>) run_advance<KIND>(P, B, nb, cb, tb);
       }
     }
   }
