@@ -5,6 +5,8 @@
         --problem poisson3d7 --grid 512 --variant merged --json-out run.json
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 -m cuda_mpi_parallel_b200 \
         --problem poisson2d5 --grid 64 64 --device cpu       # BASELINE config 1 (gloo, no GPU)
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 -m cuda_mpi_parallel_b200 \
+        --problem csr:matrix.mtx --x-out x.txt               # general CSR in row blocks over the GPUs
 
 Same controls and output contract as ``bin/cgb200`` (which drives all GPUs from one process): with no
 arguments it solves the reference's 3x3 system and prints what CUDACG.cu prints (CUDACG.cu:361-365);
@@ -24,7 +26,9 @@ import numpy as np
 
 def parse(argv=None):
     ap = argparse.ArgumentParser(prog="python -m cuda_mpi_parallel_b200")
-    ap.add_argument("--problem", default="ref3x3", choices=["ref3x3", "poisson2d5", "poisson3d7", "stencil3d27"])
+    ap.add_argument("--problem", default="ref3x3",
+                    help="ref3x3 | poisson2d5 | poisson3d7 | stencil3d27 | csr:<file.mtx> (general CSR from a Matrix "
+                         "Market file) | csr-<stencil> (the stencil operator assembled as a general CSR matrix)")
     ap.add_argument("--n", "--grid", dest="n", type=int, nargs="+", default=[64],
                     help="grid extents; use the spelling --grid under torchrun (its parser claims --n*)")
     ap.add_argument("--device", default="cuda", choices=["cuda", "cpu"])
@@ -51,11 +55,21 @@ def main(argv=None) -> int:
 
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     dims = a.n * (3 if len(a.n) == 1 else 1)
-    prob = Problem.from_name(a.problem, dims)
+    if a.problem.startswith("csr:"):                         # the reference's operand: a general CSR matrix
+        prob = Problem.from_matrix_market(a.problem[4:])
+    elif a.problem.startswith("csr-"):
+        prob = Problem.csr(*Problem.from_name(a.problem[4:], dims).to_csr())
+    elif a.problem in ("ref3x3", "poisson2d5", "poisson3d7", "stencil3d27"):
+        prob = Problem.from_name(a.problem, dims)
+    else:
+        raise SystemExit(f"unknown problem {a.problem!r}")
     rhs, _, seed = a.rhs.partition(":")
-    b = prob.rhs("default") if a.problem == "ref3x3" else prob.rhs(rhs, seed=int(seed or 0)) if prob.n <= 1 << 22 else None
-    if prob.is_csr and world > 1:
-        raise SystemExit("the reference problem / general CSR runs on one rank")
+    # (stencil problems beyond 4 M unknowns generate their right-hand side on the device instead)
+    b = (prob.rhs("default") if a.problem == "ref3x3"
+         else prob.rhs(rhs, seed=int(seed or 0)) if prob.n <= 1 << 22 or prob.is_csr else None)
+    if prob.is_csr and world > 1 and (a.device == "cpu" or prob.n < world):
+        # row-block distributed CSR exists on the GPU path only (cgb_ctx_create_csr_dist)
+        raise SystemExit("general CSR on several ranks needs --device cuda and at least one row per rank")
 
     import torch.distributed as dist
     if world > 1:
@@ -88,7 +102,7 @@ def main(argv=None) -> int:
         if b is None:
             sol.set_rhs(rhs, seed=int(seed or 0))            # generated on the device
         else:
-            sol.set_rhs(b if prob.is_csr else scatter_global(prob, part, b))
+            sol.set_rhs(scatter_global(prob, part, b))       # a row block for CSR, the owned box for stencils
         res = sol.solve(tol=a.tol, maxit=a.maxit, tol_mode=a.tol_mode, variant=a.variant, spmv=a.spmv, chunk=a.chunk,
                         use_graph={"chunk": True, "while": "while", "off": False}[a.graph])
         iters, status, r0, rn, ms, launches = res.iters, res.status, res.r0norm, res.rnorm, res.device_ms, res.launches

@@ -170,3 +170,48 @@ def test_gpu_distributed_csr_from_the_cli(cli, tmp_path):
     assert r.returncode == 0 and r.stdout == "Success\n", r.stdout + r.stderr
     x = np.loadtxt(xo)
     np.testing.assert_allclose(A @ x, np.ones(prob.n), atol=1e-7)
+
+
+def test_python_module_cli_general_csr_cpu(tmp_path):
+    # python -m ... --problem csr:<file> / csr-<stencil>: the reference's operand type; several CPU ranks are refused
+    import os
+    import sys
+    import scipy.io
+    env = dict(os.environ, OMP_NUM_THREADS="1")
+    prob = Problem.poisson3d(9, 8, 7)
+    A = prob.to_scipy()
+    m, xo = tmp_path / "p.mtx", tmp_path / "x.txt"
+    scipy.io.mmwrite(str(m), A, symmetry="general")
+    for spec in (f"csr:{m}", "csr-poisson3d7"):
+        r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--device", "cpu", "--problem", spec, "--grid", "9", "8",
+                            "7", "--tol", "1e-10", "--x-out", str(xo)], capture_output=True, text=True, timeout=300, env=env)
+        assert r.returncode == 0 and r.stdout == "Success\n", r.stdout + r.stderr
+        np.testing.assert_allclose(A @ np.loadtxt(xo), np.ones(prob.n), atol=1e-8)
+    r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--device", "cpu", "--problem", "nonsense"],
+                       capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode != 0 and "unknown problem" in r.stderr
+    r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--device", "cpu", "--problem", f"csr:{m}"],
+                       capture_output=True, text=True, timeout=300, env=dict(env, RANK="0", WORLD_SIZE="2"))
+    assert r.returncode != 0 and "general CSR on several ranks" in r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_python_module_cli_distributed_csr_gpu(tmp_path):
+    # the same through torchrun, one rank per GPU: row blocks, remote entries of p read over NVLink
+    import os
+    import sys
+    import scipy.io
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    prob = Problem.poisson3d(14, 12, 10)
+    A = prob.to_scipy()
+    m, xo = tmp_path / "p.mtx", tmp_path / "x.txt"
+    scipy.io.mmwrite(str(m), A, symmetry="general")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29913", "-m", "cuda_mpi_parallel_b200", "--problem", f"csr:{m}",
+                        "--tol", "1e-9", "--x-out", str(xo)], capture_output=True, text=True, timeout=300,
+                       env=dict(os.environ, CGB_TIMEOUT_MS="5000"))
+    assert r.returncode == 0 and "Success" in r.stdout, r.stdout + r.stderr
+    np.testing.assert_allclose(A @ np.loadtxt(xo), np.ones(prob.n), atol=1e-7)
