@@ -14,6 +14,7 @@ PROBLEMS = [
     Problem.poisson2d(2300, 9),                                        # 2D rows wider than one 1024-cell tile
     Problem.poisson2d(256, 40), Problem.poisson2d(1024, 33),           # 2D rows of whole 256-cell boxes: one TMA op per row
     Problem.poisson2d(2304, 21),                                       # ... 3 tiles, the last one mostly out of bounds
+    Problem.poisson3d(32, 1280, 24), Problem.stencil27(32, 1280, 24),  # 80 bands x 3 z chunks = 240 items on 148 CTAs
 ]
 
 

@@ -296,6 +296,23 @@ def test_2d_problems_on_the_tma_kernels(prob, variant):
     np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-6 * max(1.0, np.abs(ref.x).max()))
 
 
+@pytest.mark.parametrize("variant", ["fused", "recompute", "merged"])
+@pytest.mark.parametrize("prob", [Problem.poisson3d(32, 1280, 24), Problem.stencil27(32, 1280, 24)],
+                         ids=lambda p: f"{p.name}-{'x'.join(map(str, p.dims))}")
+def test_several_items_per_cta(prob, variant):
+    # 80 bands x 3 z chunks = 240 (band, chunk) items on at most 148 CTAs: CTAs run one or two items back to back
+    # through the same stage ring (tests/test_tma_geometry.py pins the decomposition)
+    b = prob.rhs("random", seed=13)
+    K = 40
+    ref = cpu_cg(prob, b, tol=1e-30, maxit=K)
+    s = CGSolver(prob)
+    s.set_rhs(b)
+    res = s.solve(fixed_iters=K, variant=variant, spmv="tma", chunk=9)
+    assert res.iters == K and res.status in (0, 2)
+    np.testing.assert_allclose(s.history(K), ref.history[:K], rtol=1e-8)
+    np.testing.assert_allclose(s.x().cpu().numpy(), ref.x, atol=1e-8 * max(1.0, np.abs(ref.x).max()))
+
+
 def test_iterate_streamed_copies_each_residual_to_pinned_memory():
     import torch
     prob = Problem.poisson3d(40, 36, 44)

@@ -61,6 +61,9 @@ def test_z_split_uses_all_sms_when_one_round_would_leave_them_idle():
     # 1024^3: 512 bands = 3.46 rounds; two z chunks make it 6.92
     g, _ = geo(Problem.poisson3d(1024), mode=5)
     assert (g["nbands"], g["zs"], g["grid"]) == (512, 2, 148)
+    # a small tall grid used by the GPU tests to run several items per CTA
+    g, _ = geo(Problem.poisson3d(32, 1280, 24), mode=5)
+    assert (g["nbands"], g["zs"], g["nitems"], g["grid"]) == (80, 3, 240, 148)
     # the headline grid keeps its single round (measured: a finer split is 7-10 % slower there)
     for mode in (0, 4, 5):
         g, _ = geo(Problem.poisson3d(512), mode=mode)
