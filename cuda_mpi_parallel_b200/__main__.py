@@ -7,6 +7,7 @@
         --problem poisson2d5 --grid 64 64 --device cpu       # BASELINE config 1 (gloo, no GPU)
     python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 -m cuda_mpi_parallel_b200 \
         --problem csr:matrix.mtx --x-out x.txt               # general CSR in row blocks over the GPUs
+                                                             # (--device cpu: the same over gloo)
 
 Same controls and output contract as ``bin/cgb200`` (which drives all GPUs from one process): with no
 arguments it solves the reference's 3x3 system and prints what CUDACG.cu prints (CUDACG.cu:361-365);
@@ -67,9 +68,8 @@ def main(argv=None) -> int:
     # (stencil problems beyond 4 M unknowns generate their right-hand side on the device instead)
     b = (prob.rhs("default") if a.problem == "ref3x3"
          else prob.rhs(rhs, seed=int(seed or 0)) if prob.n <= 1 << 22 or prob.is_csr else None)
-    if prob.is_csr and world > 1 and (a.device == "cpu" or prob.n < world):
-        # row-block distributed CSR exists on the GPU path only (cgb_ctx_create_csr_dist)
-        raise SystemExit("general CSR on several ranks needs --device cuda and at least one row per rank")
+    if prob.is_csr and prob.n < world:
+        raise SystemExit("general CSR in row blocks needs at least one row per rank")
 
     import torch.distributed as dist
     if world > 1:

@@ -89,9 +89,61 @@ def _halo_exchange(box: _Box, v, parts, group):
         V[gz, gy, :L.nx] = buf.numpy()
 
 
+def _cpu_dist_cg_csr(problem, b_local, group, tol, maxit, tol_mode) -> DistSolve:
+    """General CSR (the operand of CUDACG.cu:213-216) in row blocks: there is no geometric halo, so every iteration
+    all-gathers p (rank order = row order) and multiplies the rank's rows by it - the CPU counterpart of the GPU
+    path's remote loads of p (cgb_ctx_create_csr_dist)."""
+    import scipy.sparse as sp
+    import torch
+    import torch.distributed as dist
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    part = make_partition(problem, world, rank, 1)
+    r0_, r1_ = part.x0, part.x0 + part.nx
+    e0, e1 = int(problem.rowptr[r0_]), int(problem.rowptr[r1_])
+    A = sp.csr_matrix((problem.val[e0:e1], problem.colind[e0:e1], problem.rowptr[r0_:r1_ + 1] - e0),
+                      shape=(part.nx, problem.n))
+    counts = [make_partition(problem, world, q, 1).nx for q in range(world)]
+
+    cmax = max(counts)
+
+    def gather(v):
+        mine = torch.zeros(cmax, dtype=torch.float64)       # row blocks differ by at most one row: pad to the largest
+        mine[:part.nx] = torch.from_numpy(np.ascontiguousarray(v))
+        parts = [torch.empty(cmax, dtype=torch.float64) for _ in counts]
+        dist.all_gather(parts, mine, group=group)
+        return np.concatenate([t.numpy()[:c] for t, c in zip(parts, counts)])
+
+    x = np.zeros(part.nx)
+    r = np.array(b_local, dtype=np.float64).reshape(-1)
+    if r.size != part.nx:
+        raise ValueError(f"rank {rank} owns {part.nx} rows, b_local has {r.size}")
+    p = r.copy()
+    rn = float(np.sqrt(_allsum([float(r @ r)], group)[0]))
+    rho, r0 = rn * rn, rn
+    thresh = tol * rn if tol_mode == "rel" else tol
+    hist, iters, conv = [], 0, False
+    for it in range(maxit):
+        Ap = A @ gather(p)
+        alpha = rho / _allsum([float(p @ Ap)], group)[0]
+        x += alpha * p
+        r -= alpha * Ap
+        rhop = rho
+        rn = float(np.sqrt(_allsum([float(r @ r)], group)[0]))
+        hist.append(rn)
+        iters = it + 1
+        if rn < thresh:
+            conv = True
+            break
+        rho = rn * rn
+        p = r + (rho / rhop) * p
+    return DistSolve(x, iters, conv, r0, rn, np.array(hist))
+
+
 def cpu_dist_cg(problem, b_local: np.ndarray, group=None, tol: float = 1e-7, maxit: int = 2000,
                 tol_mode: str = "abs", decomp: int = 1) -> DistSolve:
     import torch.distributed as dist
+    if problem.is_csr:
+        return _cpu_dist_cg_csr(problem, b_local, group, tol, maxit, tol_mode)
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     part = make_partition(problem, world, rank, decomp)
     lay = make_layout(problem, part)

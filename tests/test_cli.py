@@ -190,9 +190,12 @@ def test_python_module_cli_general_csr_cpu(tmp_path):
     r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--device", "cpu", "--problem", "nonsense"],
                        capture_output=True, text=True, timeout=300, env=env)
     assert r.returncode != 0 and "unknown problem" in r.stderr
-    r = subprocess.run([sys.executable, "-m", "cuda_mpi_parallel_b200", "--device", "cpu", "--problem", f"csr:{m}"],
-                       capture_output=True, text=True, timeout=300, env=dict(env, RANK="0", WORLD_SIZE="2"))
-    assert r.returncode != 0 and "general CSR on several ranks" in r.stderr
+    # two CPU ranks over gloo: row blocks, p all-gathered every iteration
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29915", "-m", "cuda_mpi_parallel_b200", "--device", "cpu", "--problem",
+                        f"csr:{m}", "--tol", "1e-10", "--x-out", str(xo)], capture_output=True, text=True, timeout=300, env=env)
+    assert r.returncode == 0 and "Success" in r.stdout, r.stdout + r.stderr
+    np.testing.assert_allclose(A @ np.loadtxt(xo), np.ones(prob.n), atol=1e-8)
 
 
 @pytest.mark.gpu

@@ -21,9 +21,10 @@ def _run(nproc, args, port, timeout=300):
 
 
 @pytest.mark.parametrize("nproc,name,dims,decomp", [(2, "poisson2d5", "64x64", 1), (4, "poisson3d7", "10x12x16", 2),
-                                                    (4, "stencil3d27", "8x10x12", 2)])
+                                                    (4, "stencil3d27", "8x10x12", 2), (3, "csr-stencil3d27", "7x6x5", 1),
+                                                    (2, "csr-poisson2d5", "31x17", 1)])
 def test_cpu_distributed_cg_gloo(nproc, name, dims, decomp):
-    # BASELINE config 1: 2D 5-pt 64x64, 2 ranks, CPU path.
+    # BASELINE config 1: 2D 5-pt 64x64, 2 ranks, CPU path. csr-*: general CSR in (uneven) row blocks, p all-gathered.
     res = _run(nproc, ["cpu", name, dims, str(decomp)], port=29600 + nproc + decomp)
     assert res["ok"] and res["ranks_identical"], res
 
