@@ -74,3 +74,47 @@ def test_csr_has_no_tma_path():
     p = Problem.poisson2d(12, 10)
     rowptr, colind, val = p.to_csr()
     assert geo(Problem.csr(rowptr, colind, val))[0] is None
+
+
+# ---- property test: any grid / rank count / mode gives a decomposition that covers the box and fits the chip ----
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@st.composite
+def _geo_cases(draw):
+    kind = draw(st.sampled_from(["poisson2d5", "poisson3d7", "stencil3d27"]))
+    nx = draw(st.sampled_from([1, 7, 33, 256, 384, 512, 1030, 2304, 4096]))
+    ny = draw(st.integers(1, 1500))
+    nz = draw(st.integers(1, 1100))
+    nranks = draw(st.sampled_from([1, 2, 3, 8]))
+    return kind, nx, ny, nz, nranks, draw(st.integers(0, 7)), draw(st.sampled_from([0, 1, 4, 5])), draw(st.sampled_from([147, 148]))
+
+
+@given(_geo_cases())
+@settings(max_examples=300, deadline=None)
+def test_geometry_properties(case):
+    kind, nx, ny, nz, nranks, rank, mode, nsm = case
+    prob = Problem.from_name(kind, [nx, ny, nz])
+    rank %= nranks
+    try:
+        g, lay = geo(prob, nranks=nranks, rank=rank, mode=mode, nsm=nsm)
+    except Exception:
+        return                                            # more ranks than planes: the partition is refused
+    if g is None:
+        return                                            # (no stage fits: the solver falls back to the L1-path kernels)
+    tile = 2 * g["LX"]
+    assert g["ntx"] * tile >= lay.nx and (g["ntx"] - 1) * tile < lay.nx
+    assert g["nby"] * g["RB"] >= lay.ny and (g["nby"] - 1) * g["RB"] < lay.ny
+    assert g["zs"] * g["zchunk"] >= lay.nz and (g["zs"] - 1) * g["zchunk"] < lay.nz and g["zchunk"] >= 1
+    assert g["nitems"] == g["ntx"] * g["nby"] * g["zs"]
+    assert 1 <= g["grid"] <= nsm and 0 <= g["nhalo"] <= 24
+    sweepers = g["grid"] - g["nhalo"]
+    assert 1 <= sweepers <= g["nitems"]                   # no sweeping CTA without an item
+    assert 2 <= g["nstages"] <= 8 and g["nstages"] * g["stage_bytes"] <= 200 * 1024
+    # the chosen split is never predicted slower than one item per CTA (rounds x (planes per item + 2))
+    rounds = -(-g["nitems"] // sweepers) if g["nhalo"] == 0 else -(-g["nitems"] // sweepers)
+    one = max(1, min(nsm // g["nbands"], max(1, lay.nz // 8)))
+    zc1 = -(-lay.nz // one)
+    one_cost = -(-(g["nbands"] * -(-lay.nz // zc1)) // nsm) * (zc1 + 2)
+    if g["nhalo"] == 0 and not (mode == 5 and g["zs"] == 2 and one == 1):   # (two half sweeps of a middle rank: forced)
+        assert rounds * (g["zchunk"] + 2) <= one_cost
