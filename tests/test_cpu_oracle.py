@@ -106,3 +106,36 @@ def test_rhs_fill_box_matches_the_per_entry_generator_and_partitions():
             parts = [make_partition(prob, nranks, r, decomp) for r in range(nranks)]
             locs = [prob.rhs_local(p, "random", seed=3) for p in parts]
             np.testing.assert_array_equal(gather_global(prob, parts, locs), g)
+
+
+def test_csr_constructors_reject_malformed_input_before_touching_the_gpu():
+    # A bad offset or column index would make the SpMV read out of bounds on the device (over peer mappings when
+    # distributed), so both CSR constructors validate on the host first: this runs without a GPU.
+    import ctypes as C
+    from cuda_mpi_parallel_b200 import _native as N, make_partition
+    L = N.lib()
+    good_rp = np.array([0, 2, 3, 5], dtype=np.int32)
+    good_ci = np.array([0, 2, 1, 0, 2], dtype=np.int32)
+    val = np.ones(5)
+
+    def create(rp, ci, nnz=5, hist_cap=16):
+        ctx = C.c_void_p()
+        return L.cgb_ctx_create_csr(3, nnz, rp.ctypes.data, ci.ctypes.data, val.ctypes.data, 0, hist_cap, C.byref(ctx))
+
+    cases = {"rowptr[0]": (np.array([1, 2, 3, 5], dtype=np.int32), good_ci, {}),
+             "not monotone": (np.array([0, 3, 2, 5], dtype=np.int32), good_ci, {}),
+             "does not match nnz": (np.array([0, 2, 3, 4], dtype=np.int32), good_ci, {}),
+             "column index": (good_rp, np.array([0, 3, 1, 0, 2], dtype=np.int32), {}),
+             "column index ": (good_rp, np.array([0, -1, 1, 0, 2], dtype=np.int32), {}),
+             "hist_cap": (good_rp, good_ci, {"hist_cap": 0})}
+    for what, (rp, ci, kw) in cases.items():
+        rc = create(rp, ci, **kw)
+        assert rc < 0, what
+        assert what.strip() in L.cgb_last_error().decode(), (what, L.cgb_last_error())
+    # the distributed constructor checks columns against the GLOBAL row count and the block against the partition
+    prob = Problem.csr(good_rp, good_ci, val)
+    part = make_partition(prob, 3, 1)                     # rank 1 owns row 1: one entry
+    ctx = C.c_void_p()
+    rp1, ci_bad = np.array([0, 1], dtype=np.int32), np.array([3], dtype=np.int32)
+    rc = L.cgb_ctx_create_csr_dist(3, C.byref(part), 1, rp1.ctypes.data, ci_bad.ctypes.data, val.ctypes.data, 0, 16, C.byref(ctx))
+    assert rc < 0 and "column index" in L.cgb_last_error().decode()
