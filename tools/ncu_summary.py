@@ -6,6 +6,7 @@
 import csv
 import io
 import json
+import re
 import subprocess
 import sys
 from pathlib import Path
@@ -17,11 +18,15 @@ WANT = [
     "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
     "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "lts__t_bytes.sum",
     "l1tex__t_bytes.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
-    "smsp__warp_issue_stalled_long_scoreboard_per_warp_active.pct",
-    "smsp__warp_issue_stalled_barrier_per_warp_active.pct",
-    "smsp__warp_issue_stalled_membar_per_warp_active.pct",
     "launch__shared_mem_per_block_dynamic", "launch__shared_mem_per_block_static",
+    # issue-boundness (profiles/ROOFLINE.md R2.6): instructions, issue-slot utilisation, fp64 pipe, top stall reasons
+    "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active", "sm__cycles_active.avg",
+    "smsp__inst_executed_op_tma_ld.sum", "smsp__average_warp_latency_per_inst_issued.ratio",
 ]
+
+
+STALL = re.compile(r"smsp__average_warps_issue_stalled_(\w+)_per_issue_active\.ratio$")
 
 
 def main():
@@ -41,6 +46,17 @@ def main():
         for w in WANT:
             if w in d:
                 lines.append(f"| `{w}` | {d[w]} | {units[hdr.index(w)]} |")
+        # warp states: average number of warps per scheduler in each stall state per issue cycle, largest first
+        stalls = []
+        for k in hdr:
+            m = STALL.match(k)
+            if m and d.get(k):
+                try:
+                    stalls.append((float(d[k].replace(",", "")), m.group(1)))
+                except ValueError:
+                    pass
+        for v, name in sorted(stalls, reverse=True)[:6]:
+            lines.append(f"| warps stalled: `{name}` (per issue-active cycle) | {v:.2f} | warps |")
         try:
             dur = float(d["gpu__time_duration.sum"].replace(",", ""))
             unit = units[hdr.index("gpu__time_duration.sum")]
