@@ -2,6 +2,7 @@
 # The reference's build recipe is one line in a comment: nvcc CUDACG.cu -lcublas -lcusparse (CUDACG.cu:1).
 #
 #   make            libcgb200.so + bin/cgb200
+#   make examples   bin/poisson3d (plain C on the C ABI)
 #   make baselines  libcgb200_baseline.so (B3) + bin/refstyle_b4 (B4; needs the system libnccl)
 #   make OUT=/tmp/x out-of-tree objects and products
 NVCC    ?= nvcc
@@ -43,7 +44,13 @@ $(BINDIR)/refstyle_b4: baseline/src/ref_b4_main.cu include/cgb200.h $(LIBDIR)/li
 	$(NVCC) $(ARCH) -O3 -std=c++17 -lineinfo -Iinclude $< -o $@ -L$(LIBDIR) -lcgb200 -lnccl -lcusparse -lcublas -lpthread \
 	    -Xlinker -rpath -Xlinker '$$ORIGIN/../cuda_mpi_parallel_b200/lib'
 
+examples: $(BINDIR)/poisson3d
+
+$(BINDIR)/poisson3d: examples/poisson3d.c include/cgb200.h $(LIBDIR)/libcgb200.so
+	@mkdir -p $(BINDIR)
+	$(CC) -std=c99 -O2 -Wall -Iinclude $< -o $@ -L$(LIBDIR) -lcgb200 '-Wl,-rpath,$$ORIGIN/../cuda_mpi_parallel_b200/lib' -lm
+
 clean:
 	rm -rf $(OBJDIR)
 
-.PHONY: all baselines clean
+.PHONY: all baselines examples clean

@@ -1,5 +1,6 @@
 """Tier T0: the command-line front end against the reference's literal stdout."""
 import json
+import re
 import subprocess
 
 import numpy as np
@@ -218,3 +219,24 @@ def test_python_module_cli_distributed_csr_gpu(tmp_path):
                        env=dict(os.environ, CGB_TIMEOUT_MS="5000"))
     assert r.returncode == 0 and "Success" in r.stdout, r.stdout + r.stderr
     np.testing.assert_allclose(A @ np.loadtxt(xo), np.ones(prob.n), atol=1e-7)
+
+
+def test_c_example_compiles_as_c99_and_runs_on_the_host_oracle(tmp_path):
+    # include/cgb200.h must stay a valid C header; examples/poisson3d.c is the reference's program flow on the C ABI
+    import shutil
+    from cuda_mpi_parallel_b200.utils import build
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    build.build_core()
+    exe = tmp_path / "poisson3d"
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", f"-I{build.ROOT / 'include'}",
+                        str(build.ROOT / "examples" / "poisson3d.c"), "-o", str(exe), f"-L{build.LIBDIR}", "-lcgb200",
+                        f"-Wl,-rpath,{build.LIBDIR}", "-lm"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([str(exe), "20", "--cpu"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and r.stdout.endswith("Success\n"), r.stdout + r.stderr
+    m = re.search(r"(\d+) iterations, \|\|r\|\| = (\S+) \(recomputed (\S+)\)", r.stdout)
+    prob = Problem.poisson3d(20)
+    assert int(m.group(1)) == cpu_cg(prob, prob.rhs("ones")).iters
+    assert float(m.group(2)) < 1e-7 and float(m.group(3)) < 2e-7
